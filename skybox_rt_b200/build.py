@@ -1,0 +1,91 @@
+"""In-tree native build of the B200 back-end.
+
+    python -m skybox_rt_b200.build            # build what is stale
+    python -m skybox_rt_b200.build --force
+
+Outputs (git-ignored, shipped to the GPU box with the repo snapshot):
+    skybox_rt_b200/lib/libvortex.so           vx_* C ABI + CUDA kernels (sm_100a), nvcc
+    skybox_rt_b200/lib/libvortex-cuda.so      same file under the reference's plugin name
+    skybox_rt_b200/lib/libskybox_rt_host.so   host pre-pass (scenes, BVH2 builder), gcc, no CUDA
+    skybox_rt_b200/bin/raytrace               the regression app (C host program)
+"""
+import os
+import shutil
+import subprocess
+import sys
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG)
+CSRC = os.path.join(PKG, "csrc")
+LIB = os.path.join(PKG, "lib")
+BIN = os.path.join(PKG, "bin")
+INC = os.path.join(ROOT, "include")
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+CC = os.environ.get("CC", "gcc")
+
+# -fmad=false etc.: the bit-exactness contract of csrc/rt_device.cuh
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-Wall",
+    "-I", INC, "-I", CSRC,
+]
+HOST_CFLAGS = ["-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-Wall", "-Wextra", "-I", INC]
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def _glob(d, exts):
+    out = []
+    for base, _, files in os.walk(d):
+        for f in sorted(files):
+            if f.endswith(exts):
+                out.append(os.path.join(base, f))
+    return out
+
+
+def _run(cmd, verbose):
+    if verbose:
+        print(" ".join(cmd), flush=True)
+    subprocess.run(cmd, check=True)
+
+
+def build(force=False, verbose=False):
+    os.makedirs(LIB, exist_ok=True)
+    os.makedirs(BIN, exist_ok=True)
+    headers = _glob(INC, (".h",)) + _glob(CSRC, (".h", ".cuh"))
+
+    # 1. host pre-pass library (plain C)
+    host_src = _glob(os.path.join(CSRC, "host"), (".c",))
+    host_so = os.path.join(LIB, "libskybox_rt_host.so")
+    if force or _stale(host_so, host_src + headers):
+        _run([CC] + HOST_CFLAGS + ["-shared", "-o", host_so] + host_src + ["-lm"], verbose)
+
+    # 2. the CUDA back-end
+    cu_src = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cpp"))]
+    vx_so = os.path.join(LIB, "libvortex.so")
+    if force or _stale(vx_so, cu_src + headers):
+        _run([NVCC] + NVCC_FLAGS + ["-shared", "-o", vx_so] + cu_src, verbose)
+    plugin = os.path.join(LIB, "libvortex-cuda.so")
+    if force or _stale(plugin, [vx_so]):
+        shutil.copyfile(vx_so, plugin)
+
+    # 3. the regression app
+    app_dir = os.path.join(PKG, "apps", "raytrace")
+    app_src = _glob(app_dir, (".c",)) if os.path.isdir(app_dir) else []
+    if app_src:
+        exe = os.path.join(BIN, "raytrace")
+        if force or _stale(exe, app_src + headers + [vx_so, host_so]):
+            _run([CC, "-O2", "-ffp-contract=off", "-Wall", "-Wextra", "-I", INC, "-o", exe] + app_src +
+                 ["-L", LIB, "-lvortex", "-lskybox_rt_host", "-lz", "-lm", "-Wl,-rpath,$ORIGIN/../lib"], verbose)
+    return {"vortex": vx_so, "host": host_so}
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv, verbose=True)

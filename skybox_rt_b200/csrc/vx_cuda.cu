@@ -1,0 +1,338 @@
+// vx_cuda.cu -- the vx_* host API over the CUDA runtime (libvortex.so for B200).
+//
+// Each function reproduces the argument checks, return codes and ordering rules of the reference
+// path  stub forwarder -> callbacks_t lambda -> vx_device method :
+//   runtime/stub/vortex.cpp:58-182, runtime/common/callbacks.inc:20-225,
+//   runtime/simx/vortex.cpp:32-246 (the driver used as the behavioural template).
+// No CPU fallback: without a usable CUDA device vx_dev_open fails.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include <new>
+
+#include "vx_internal.h"
+
+namespace srt {
+int rt_read_counters(vx_device* dev);
+}
+
+namespace {
+
+inline vx_device* as_dev(vx_device_h h) { return reinterpret_cast<vx_device*>(h); }
+inline vx_buffer* as_buf(vx_buffer_h h) { return reinterpret_cast<vx_buffer*>(h); }
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  if (!v || !*v) return dflt;
+  return atoi(v);
+}
+
+// first OM DCR + 18 == end of every range the reference decodes (hw/rtl/VX_types.vh:22-28,
+// :332-340, :352-359, :439-458 with VX_TEX_LOD_MAX = 15)
+constexpr uint32_t kRefDcrBegin = 0x001;
+constexpr uint32_t kRefDcrEnd = 0x006 + (6 + 16) + 6 + 18;
+
+bool dcr_addr_ok(uint32_t addr) {
+  return (addr >= kRefDcrBegin && addr < kRefDcrEnd) || (addr >= VX_DCR_RT_BASE && addr < VX_DCR_RT_END);
+}
+
+void unlink_buffer(vx_buffer* b) {
+  vx_device* d = b->dev;
+  if (b->prev) b->prev->next = b->next; else d->buffers = b->next;
+  if (b->next) b->next->prev = b->prev;
+  d->bytes_used -= b->size;
+}
+
+int destroy_buffer(vx_buffer* b) {
+  unlink_buffer(b);
+  cudaError_t e = cudaFree(b->dptr);
+  free(b->shadow);
+  delete b;
+  return e == cudaSuccess ? 0 : -1;
+}
+
+int alloc_buffer(vx_device* dev, uint64_t size, int flags, uint64_t reported, vx_buffer** out) {
+  void* p = nullptr;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaMalloc(&p, size));
+  vx_buffer* b = new (std::nothrow) vx_buffer();
+  if (!b) { cudaFree(p); return -1; }
+  b->dev = dev;
+  b->dptr = p;
+  b->size = size;
+  b->reported_addr = reported ? reported : (uint64_t)(uintptr_t)p;
+  b->flags = flags;
+  b->shadow = size <= kShadowMaxBytes ? (uint8_t*)calloc(1, size) : nullptr;
+  b->generation = 0;
+  b->prev = nullptr;
+  b->next = dev->buffers;
+  if (dev->buffers) dev->buffers->prev = b;
+  dev->buffers = b;
+  dev->bytes_used += size;
+  *out = b;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// ------------------------------------------------------------------------------- device
+int vx_dev_open(vx_device_h* hdevice) {
+  if (nullptr == hdevice) return -1;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+    fprintf(stderr, "[VXDRV] no CUDA device: the B200 back-end has no CPU fallback\n");
+    return 1;  // same code the stub returns when the driver cannot be loaded (stub/vortex.cpp:67-78)
+  }
+  int ordinal = env_int("VX_CUDA_DEVICE", env_int("LOCAL_RANK", 0));
+  if (ordinal < 0 || ordinal >= count) ordinal = ordinal % count;
+  vx_device* dev = new (std::nothrow) vx_device();
+  if (!dev) return -1;
+  dev->cuda_dev = ordinal;
+  dev->buffers = nullptr;
+  dev->bytes_used = 0;
+  dev->rt = nullptr;
+  dev->run_recorded = false;
+  dev->last_rays_primary = 0;
+  dev->last_counters_valid = false;
+  dev->last_pipeline = 0;
+  memset(dev->last_counters, 0, sizeof(dev->last_counters));
+  if (cudaSetDevice(ordinal) != cudaSuccess || cudaGetDeviceProperties(&dev->prop, ordinal) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&dev->ev_start) != cudaSuccess || cudaEventCreate(&dev->ev_stop) != cudaSuccess) {
+    fprintf(stderr, "[VXDRV] cannot initialise CUDA device %d: %s\n", ordinal, cudaGetErrorString(cudaGetLastError()));
+    delete dev;
+    return -1;
+  }
+  *hdevice = dev;
+  return 0;
+}
+
+int vx_dev_close(vx_device_h hdevice) {
+  if (nullptr == hdevice) return -1;
+  vx_device* dev = as_dev(hdevice);
+  cudaSetDevice(dev->cuda_dev);
+  cudaStreamSynchronize(dev->stream);
+  if (env_int("VORTEX_PROFILING", 0) != 0) vx_dump_perf(hdevice, stdout);  // stub/vortex.cpp:99-104
+  srt::rt_destroy(dev);
+  while (dev->buffers) destroy_buffer(dev->buffers);  // apps leak their per-draw args buffers
+  cudaEventDestroy(dev->ev_start);
+  cudaEventDestroy(dev->ev_stop);
+  cudaStreamDestroy(dev->stream);
+  delete dev;
+  return 0;
+}
+
+int vx_dev_caps(vx_device_h hdevice, uint32_t caps_id, uint64_t* value) {
+  if (nullptr == hdevice || nullptr == value) return -1;
+  const vx_device* dev = as_dev(hdevice);
+  switch (caps_id) {
+    case VX_CAPS_VERSION: *value = 100; break;  // sm_100a
+    case VX_CAPS_NUM_THREADS: *value = (uint64_t)dev->prop.warpSize; break;
+    case VX_CAPS_NUM_WARPS: *value = (uint64_t)(dev->prop.maxThreadsPerMultiProcessor / dev->prop.warpSize); break;
+    case VX_CAPS_NUM_CORES: *value = (uint64_t)dev->prop.multiProcessorCount; break;
+    case VX_CAPS_CACHE_LINE_SIZE: *value = 128; break;
+    case VX_CAPS_GLOBAL_MEM_SIZE: *value = (uint64_t)dev->prop.totalGlobalMem; break;
+    case VX_CAPS_LOCAL_MEM_SIZE: *value = (uint64_t)dev->prop.sharedMemPerMultiprocessor; break;
+    case VX_CAPS_ISA_FLAGS:
+      *value = VX_ISA_STD_A | VX_ISA_STD_F | VX_ISA_STD_D | VX_ISA_STD_I | VX_ISA_EXT_ICACHE | VX_ISA_EXT_DCACHE |
+               VX_ISA_EXT_L2CACHE | VX_ISA_EXT_LMEM | VX_ISA_EXT_RT;
+      break;
+    default:
+      fprintf(stderr, "[VXDRV] invalid caps id: %u\n", caps_id);
+      return -1;
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------- memory
+int vx_mem_alloc(vx_device_h hdevice, uint64_t size, int flags, vx_buffer_h* hbuffer) {
+  if (nullptr == hdevice || nullptr == hbuffer || 0 == size) return -1;
+  vx_buffer* b;
+  if (alloc_buffer(as_dev(hdevice), size, flags, 0, &b) != 0) return -1;
+  *hbuffer = b;
+  return 0;
+}
+
+int vx_mem_reserve(vx_device_h hdevice, uint64_t address, uint64_t size, int flags, vx_buffer_h* hbuffer) {
+  if (nullptr == hdevice || nullptr == hbuffer || 0 == size) return -1;
+  vx_buffer* b;
+  if (alloc_buffer(as_dev(hdevice), size, flags, address, &b) != 0) return -1;
+  *hbuffer = b;
+  return 0;
+}
+
+int vx_mem_free(vx_buffer_h hbuffer) {
+  if (nullptr == hbuffer) return 0;  // callbacks.inc:100-103
+  vx_buffer* b = as_buf(hbuffer);
+  cudaSetDevice(b->dev->cuda_dev);
+  cudaStreamSynchronize(b->dev->stream);  // a running kernel may still read it
+  return destroy_buffer(b);
+}
+
+int vx_mem_access(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, int flags) {
+  if (nullptr == hbuffer) return -1;
+  vx_buffer* b = as_buf(hbuffer);
+  if (offset + size > b->size) return -1;
+  b->flags = flags;
+  return 0;
+}
+
+int vx_mem_address(vx_buffer_h hbuffer, uint64_t* address) {
+  if (nullptr == hbuffer || nullptr == address) return -1;
+  *address = as_buf(hbuffer)->reported_addr;
+  return 0;
+}
+
+int vx_mem_info(vx_device_h hdevice, uint64_t* mem_free, uint64_t* mem_used) {
+  if (nullptr == hdevice) return -1;
+  vx_device* dev = as_dev(hdevice);
+  size_t f = 0, t = 0;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaMemGetInfo(&f, &t));
+  if (mem_free) *mem_free = f;
+  if (mem_used) *mem_used = dev->bytes_used;
+  return 0;
+}
+
+int vx_copy_to_dev(vx_buffer_h hbuffer, const void* host_ptr, uint64_t dst_offset, uint64_t size) {
+  if (nullptr == hbuffer || nullptr == host_ptr) return -1;
+  vx_buffer* b = as_buf(hbuffer);
+  if (dst_offset + size > b->size) return -1;  // callbacks.inc:155-156
+  vx_device* dev = b->dev;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, host_ptr, size, cudaMemcpyHostToDevice, dev->stream));
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  if (b->shadow) memcpy(b->shadow + dst_offset, host_ptr, size);
+  b->generation++;
+  return 0;
+}
+
+int vx_copy_from_dev(void* host_ptr, vx_buffer_h hbuffer, uint64_t src_offset, uint64_t size) {
+  if (nullptr == hbuffer || nullptr == host_ptr) return -1;
+  vx_buffer* b = as_buf(hbuffer);
+  if (src_offset + size > b->size) return -1;  // callbacks.inc:166-167
+  vx_device* dev = b->dev;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaMemcpyAsync(host_ptr, (const char*)b->dptr + src_offset, size, cudaMemcpyDeviceToHost, dev->stream));
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------- execution
+int vx_start(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments) {
+  if (nullptr == hdevice || nullptr == hkernel || nullptr == harguments) return -1;
+  vx_device* dev = as_dev(hdevice);
+  vx_buffer* k = as_buf(hkernel);
+  vx_buffer* args = as_buf(harguments);
+  // the kernel image is {magic, pipeline, version} (include/skybox_rt.h); it is host-written and
+  // small, so its shadow copy is authoritative
+  struct { uint64_t magic; uint32_t pipeline, version; } img;
+  if (!k->shadow || k->size < sizeof(img)) {
+    fprintf(stderr, "[VXDRV] vx_start: kernel buffer is not a pipeline descriptor\n");
+    return -1;
+  }
+  memcpy(&img, k->shadow, sizeof(img));
+  if (img.magic != SRT_KERNEL_MAGIC) {
+    fprintf(stderr, "[VXDRV] vx_start: bad kernel magic (RISC-V .vxbin images cannot run on the CUDA back-end)\n");
+    return -1;
+  }
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaEventRecord(dev->ev_start, dev->stream));
+  int rc = -1;
+  dev->last_counters_valid = false;
+  dev->last_pipeline = (int)img.pipeline;
+  switch (img.pipeline) {
+    case SRT_PIPELINE_RAYTRACE: {
+      kernel_arg_t a;
+      if (!args->shadow || args->size < sizeof(a)) {
+        fprintf(stderr, "[VXDRV] vx_start: arguments buffer too small for kernel_arg_t\n");
+        return -1;
+      }
+      memcpy(&a, args->shadow, sizeof(a));
+      rc = srt::rt_launch(dev, a);
+      break;
+    }
+    default:
+      fprintf(stderr, "[VXDRV] vx_start: unknown pipeline %u\n", img.pipeline);
+      return -1;
+  }
+  VX_CUDA_OK(cudaEventRecord(dev->ev_stop, dev->stream));
+  dev->run_recorded = (rc == 0);
+  return rc;
+}
+
+int vx_ready_wait(vx_device_h hdevice, uint64_t timeout) {
+  if (nullptr == hdevice) return -1;
+  vx_device* dev = as_dev(hdevice);
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  struct timespec t0, now;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  for (uint64_t spins = 0;; ++spins) {
+    cudaError_t e = cudaStreamQuery(dev->stream);
+    if (e == cudaSuccess) return 0;
+    if (e != cudaErrorNotReady) {
+      fprintf(stderr, "[VXDRV] device fault: %s\n", cudaGetErrorString(e));
+      return -1;
+    }
+    clock_gettime(CLOCK_MONOTONIC, &now);
+    const uint64_t ms = (uint64_t)(now.tv_sec - t0.tv_sec) * 1000ull + (uint64_t)((now.tv_nsec - t0.tv_nsec) / 1000000);
+    if (ms >= timeout) return -1;  // simx/vortex.cpp:195-209
+    if (spins > 2000) {
+      struct timespec nap = {0, 20000};
+      nanosleep(&nap, nullptr);
+    }
+  }
+}
+
+int vx_dcr_write(vx_device_h hdevice, uint32_t addr, uint32_t value) {
+  if (nullptr == hdevice) return -1;
+  if (!dcr_addr_ok(addr)) {
+    fprintf(stderr, "[VXDRV] invalid DCR write address 0x%x\n", addr);
+    return -1;
+  }
+  vx_device* dev = as_dev(hdevice);
+  // the reference blocks until the previous run completes (simx/vortex.cpp:211-218)
+  cudaSetDevice(dev->cuda_dev);
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  dev->dcrs[addr] = value;
+  return 0;
+}
+
+int vx_dcr_read(vx_device_h hdevice, uint32_t addr, uint32_t* value) {
+  if (nullptr == hdevice || nullptr == value) return -1;
+  if (!dcr_addr_ok(addr)) return -1;
+  vx_device* dev = as_dev(hdevice);
+  auto it = dev->dcrs.find(addr);
+  *value = it == dev->dcrs.end() ? 0u : it->second;
+  return 0;
+}
+
+int vx_mpm_query(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t* value) {
+  if (nullptr == hdevice || nullptr == value) return -1;
+  vx_device* dev = as_dev(hdevice);
+  (void)core_id;  // counters are device totals; every core id reports the total
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  float ms = 0.0f;
+  if (dev->run_recorded) VX_CUDA_OK(cudaEventElapsedTime(&ms, dev->ev_start, dev->ev_stop));
+  if (!dev->last_counters_valid && dev->last_pipeline == SRT_PIPELINE_RAYTRACE) srt::rt_read_counters(dev);
+  const uint64_t* c = dev->last_counters;
+  switch (addr) {
+    case VX_CSR_MCYCLE: *value = (uint64_t)((double)ms * 1e-3 * (double)dev->prop.clockRate * 1e3); break;
+    case VX_CSR_MINSTRET: *value = dev->last_rays_primary + c[CTR_RAYS_SHADOW] + c[CTR_RAYS_BOUNCE]; break;
+    case VX_CSR_RT_RAYS_PRIMARY: *value = dev->last_rays_primary; break;
+    case VX_CSR_RT_RAYS_SHADOW: *value = c[CTR_RAYS_SHADOW]; break;
+    case VX_CSR_RT_RAYS_BOUNCE: *value = c[CTR_RAYS_BOUNCE]; break;
+    case VX_CSR_RT_NODES: *value = c[CTR_NODES]; break;
+    case VX_CSR_RT_TRIS: *value = c[CTR_TRIS]; break;
+    case VX_CSR_RT_ELAPSED_NS: *value = (uint64_t)((double)ms * 1e6); break;
+    default: return -1;
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,85 @@
+// vx_internal.h -- private state of the CUDA back-end behind include/vortex.h.
+//
+// Mirrors the shape of the reference drivers: a `vx_device` object per opened device that owns
+// memory, a DCR file and the launch machinery (reference runtime/simx/vortex.cpp:32-246), and a
+// small `vx_buffer` record per allocation (reference runtime/common/callbacks.inc:14-18).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <mutex>
+
+#include "skybox_rt.h"
+#include "vortex.h"
+
+struct vx_device;
+
+struct vx_buffer {
+  vx_device* dev;
+  void* dptr;             // cudaMalloc'ed storage
+  uint64_t size;
+  uint64_t reported_addr; // == (uint64_t)dptr except for vx_mem_reserve'd kernel images
+  int flags;
+  uint8_t* shadow;        // host copy of small host-written buffers (kernel args, kernel images)
+  uint64_t generation;    // bumped by every vx_copy_to_dev (invalidates derived device data)
+  vx_buffer* prev;
+  vx_buffer* next;
+};
+
+constexpr uint64_t kShadowMaxBytes = 4096;
+
+// Device-side counters written by the kernels (one u64 each).
+enum {
+  CTR_RAYS_SHADOW = 0,
+  CTR_RAYS_BOUNCE = 1,
+  CTR_NODES = 2,
+  CTR_TRIS = 3,
+  CTR_COUNT = 8
+};
+
+namespace srt {
+struct RtState;  // rt_pipeline.cu
+}
+
+struct vx_device {
+  int cuda_dev;
+  cudaDeviceProp prop;
+  cudaStream_t stream;
+  cudaEvent_t ev_start, ev_stop;
+  bool run_recorded;            // ev_start/ev_stop bracket the last vx_start
+  std::map<uint32_t, uint32_t> dcrs;
+  vx_buffer* buffers;           // intrusive list of live allocations
+  uint64_t bytes_used;
+  srt::RtState* rt;
+  // results of the last run, filled lazily by vx_mpm_query / vx_dump_perf
+  uint64_t last_rays_primary;
+  uint64_t last_counters[CTR_COUNT];
+  bool last_counters_valid;
+  int last_pipeline;
+};
+
+// DCRs owned by this back-end (outside every range the reference decodes,
+// hw/rtl/VX_types.vh:23-29, :332-339, :353-359, :439-458).
+#define VX_DCR_RT_BASE    0x800
+#define VX_DCR_RT_VARIANT 0x800 /* 0 = default (wide BVH, wavefront), 1 = baseline BVH2 megakernel */
+#define VX_DCR_RT_STATS   0x801 /* 1 = count node fetches / triangle tests (slower)               */
+#define VX_DCR_RT_END     0x810
+
+namespace srt {
+// rt_pipeline.cu
+int rt_launch(vx_device* dev, const kernel_arg_t& arg);
+void rt_destroy(vx_device* dev);
+int rt_read_counters(vx_device* dev);
+}  // namespace srt
+
+#define VX_CUDA_OK(expr)                                                                          \
+  do {                                                                                            \
+    cudaError_t _e = (expr);                                                                      \
+    if (_e != cudaSuccess) {                                                                      \
+      fprintf(stderr, "[VXDRV] CUDA error %s at %s:%d: %s\n", cudaGetErrorName(_e), __FILE__,     \
+              __LINE__, cudaGetErrorString(_e));                                                  \
+      return -1;                                                                                  \
+    }                                                                                             \
+  } while (0)

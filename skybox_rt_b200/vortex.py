@@ -1,0 +1,191 @@
+"""ctypes binding of the vx_* C ABI (include/vortex.h) exported by skybox_rt_b200/lib/libvortex.so.
+
+Same names, argument order and error convention (0 = success) as the reference host API
+(/root/reference runtime/include/vortex.h:74-139).  The thin `Device` / `Buffer` classes below only
+turn non-zero return codes into exceptions, the way the reference apps wrap every call in RT_CHECK
+(tests/regression/draw3d/main.cpp:23-31).
+
+There is no fallback: if the native library is missing this module raises at import of `lib()`.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "lib", "libvortex.so")
+
+# caps ids / flags (include/vortex.h)
+VX_CAPS_VERSION, VX_CAPS_NUM_THREADS, VX_CAPS_NUM_WARPS, VX_CAPS_NUM_CORES = 0, 1, 2, 3
+VX_CAPS_CACHE_LINE_SIZE, VX_CAPS_GLOBAL_MEM_SIZE, VX_CAPS_LOCAL_MEM_SIZE, VX_CAPS_ISA_FLAGS = 4, 5, 6, 7
+VX_ISA_EXT_TEX, VX_ISA_EXT_RASTER, VX_ISA_EXT_OM, VX_ISA_EXT_RT = 1 << 38, 1 << 39, 1 << 40, 1 << 44
+VX_MEM_READ, VX_MEM_WRITE, VX_MEM_READ_WRITE = 1, 2, 3
+VX_MAX_TIMEOUT = 24 * 60 * 60 * 1000
+
+# counters (include/skybox_rt.h)
+VX_CSR_MCYCLE, VX_CSR_MINSTRET = 0xB00, 0xB02
+VX_CSR_RT_RAYS_PRIMARY, VX_CSR_RT_RAYS_SHADOW, VX_CSR_RT_RAYS_BOUNCE = 0x7C0, 0x7C1, 0x7C2
+VX_CSR_RT_NODES, VX_CSR_RT_TRIS, VX_CSR_RT_ELAPSED_NS = 0x7C3, 0x7C4, 0x7C5
+
+# back-end DCRs (csrc/vx_internal.h)
+VX_DCR_RT_VARIANT, VX_DCR_RT_STATS = 0x800, 0x801
+RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE = 0, 1
+
+EXPORTS = [
+    "vx_dev_open", "vx_dev_close", "vx_dev_caps", "vx_mem_alloc", "vx_mem_reserve", "vx_mem_free",
+    "vx_mem_access", "vx_mem_address", "vx_mem_info", "vx_copy_to_dev", "vx_copy_from_dev", "vx_start",
+    "vx_ready_wait", "vx_dcr_read", "vx_dcr_write", "vx_mpm_query", "vx_upload_kernel_bytes",
+    "vx_upload_kernel_file", "vx_upload_bytes", "vx_upload_file", "vx_check_occupancy", "vx_dump_perf",
+    "vx_dev_init",
+]
+
+_lib = None
+
+
+class VortexError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libvortex.so (never builds, never falls back)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise VortexError(
+                f"{LIB_PATH} is missing: run `python -m skybox_rt_b200.build` (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        vp, u32, u64, i = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
+        sig = {
+            "vx_dev_open": [C.POINTER(vp)], "vx_dev_close": [vp],
+            "vx_dev_caps": [vp, u32, C.POINTER(u64)],
+            "vx_mem_alloc": [vp, u64, i, C.POINTER(vp)],
+            "vx_mem_reserve": [vp, u64, u64, i, C.POINTER(vp)],
+            "vx_mem_free": [vp], "vx_mem_access": [vp, u64, u64, i],
+            "vx_mem_address": [vp, C.POINTER(u64)],
+            "vx_mem_info": [vp, C.POINTER(u64), C.POINTER(u64)],
+            "vx_copy_to_dev": [vp, vp, u64, u64], "vx_copy_from_dev": [vp, vp, u64, u64],
+            "vx_start": [vp, vp, vp], "vx_ready_wait": [vp, u64],
+            "vx_dcr_read": [vp, u32, C.POINTER(u32)], "vx_dcr_write": [vp, u32, u32],
+            "vx_mpm_query": [vp, u32, u32, C.POINTER(u64)],
+            "vx_upload_kernel_bytes": [vp, vp, u64, C.POINTER(vp)],
+            "vx_upload_kernel_file": [vp, C.c_char_p, C.POINTER(vp)],
+            "vx_upload_bytes": [vp, vp, u64, C.POINTER(vp)],
+            "vx_upload_file": [vp, C.c_char_p, C.POINTER(vp)],
+            "vx_check_occupancy": [vp, u32, C.POINTER(u32)],
+        }
+        for name, args in sig.items():
+            fn = getattr(L, name)
+            fn.argtypes = args
+            fn.restype = i
+        _lib = L
+    return _lib
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise VortexError(f"{what} failed with code {rc}")
+
+
+def _host_ptr(arr):
+    if isinstance(arr, (bytes, bytearray)):
+        return C.cast(C.c_char_p(bytes(arr)), C.c_void_p), len(arr)
+    if isinstance(arr, C.Structure):
+        return C.cast(C.pointer(arr), C.c_void_p), C.sizeof(arr)
+    if isinstance(arr, np.ndarray):
+        assert arr.flags["C_CONTIGUOUS"]
+        return C.c_void_p(arr.ctypes.data), arr.nbytes
+    if hasattr(arr, "data_ptr"):  # torch CPU tensor (pinned or pageable)
+        assert arr.device.type == "cpu" and arr.is_contiguous()
+        return C.c_void_p(arr.data_ptr()), arr.numel() * arr.element_size()
+    raise TypeError(type(arr))
+
+
+class Buffer:
+    def __init__(self, dev, handle, size):
+        self.dev, self.handle, self.size = dev, handle, size
+
+    @property
+    def address(self):
+        a = C.c_uint64()
+        _check(lib().vx_mem_address(self.handle, C.byref(a)), "vx_mem_address")
+        return a.value
+
+    def write(self, src, offset=0):
+        p, n = _host_ptr(src)
+        _check(lib().vx_copy_to_dev(self.handle, p, offset, n), "vx_copy_to_dev")
+
+    def read(self, dst, offset=0):
+        p, n = _host_ptr(dst)
+        _check(lib().vx_copy_from_dev(p, self.handle, offset, n), "vx_copy_from_dev")
+        return dst
+
+    def free(self):
+        if self.handle is not None:
+            _check(lib().vx_mem_free(self.handle), "vx_mem_free")
+            self.handle = None
+
+
+class Device:
+    """vx_dev_open .. vx_dev_close as a context manager."""
+
+    def __init__(self):
+        h = C.c_void_p()
+        _check(lib().vx_dev_open(C.byref(h)), "vx_dev_open")
+        self.handle = h
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def close(self):
+        if self.handle is not None:
+            _check(lib().vx_dev_close(self.handle), "vx_dev_close")
+            self.handle = None
+
+    def caps(self, caps_id):
+        v = C.c_uint64()
+        _check(lib().vx_dev_caps(self.handle, caps_id, C.byref(v)), "vx_dev_caps")
+        return v.value
+
+    def alloc(self, size, flags=VX_MEM_READ_WRITE):
+        h = C.c_void_p()
+        _check(lib().vx_mem_alloc(self.handle, size, flags, C.byref(h)), "vx_mem_alloc")
+        return Buffer(self, h, size)
+
+    def upload(self, src):
+        p, n = _host_ptr(src)
+        h = C.c_void_p()
+        _check(lib().vx_upload_bytes(self.handle, p, n, C.byref(h)), "vx_upload_bytes")
+        return Buffer(self, h, n)
+
+    def upload_kernel(self, image_bytes):
+        p, n = _host_ptr(image_bytes)
+        h = C.c_void_p()
+        _check(lib().vx_upload_kernel_bytes(self.handle, p, n, C.byref(h)), "vx_upload_kernel_bytes")
+        return Buffer(self, h, n - 16)
+
+    def start(self, kernel, args):
+        _check(lib().vx_start(self.handle, kernel.handle, args.handle), "vx_start")
+
+    def ready_wait(self, timeout_ms=VX_MAX_TIMEOUT):
+        _check(lib().vx_ready_wait(self.handle, timeout_ms), "vx_ready_wait")
+
+    def dcr_write(self, addr, value):
+        _check(lib().vx_dcr_write(self.handle, addr, value), "vx_dcr_write")
+
+    def dcr_read(self, addr):
+        v = C.c_uint32()
+        _check(lib().vx_dcr_read(self.handle, addr, C.byref(v)), "vx_dcr_read")
+        return v.value
+
+    def mpm_query(self, addr, core_id=0):
+        v = C.c_uint64()
+        _check(lib().vx_mpm_query(self.handle, addr, core_id, C.byref(v)), "vx_mpm_query")
+        return v.value
+
+    def mem_info(self):
+        f, u = C.c_uint64(), C.c_uint64()
+        _check(lib().vx_mem_info(self.handle, C.byref(f), C.byref(u)), "vx_mem_info")
+        return f.value, u.value
