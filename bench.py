@@ -1,0 +1,430 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path of BASELINE.json measured on B200 through the vx_* C ABI.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3] [--impl reference]
+
+A "step" is one frame of the workload (or one pass over the ray list for c5).  Prints ONE JSON line.
+  value   Mrays/s with the scene resident in HBM, device time from CUDA events on the launch stream
+          (L2 flushed before every timed step), max over ranks.
+  e2e     the same metric through the public host flow with HOST buffers: upload kernel_arg_t ->
+          vx_start -> vx_ready_wait -> vx_copy_from_dev(framebuffer) into pinned memory, wall clock.
+  --impl reference : the CPU oracle (oracle/, this repo's restatement -- the reference has no RT
+          code) on all host threads, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+# BASELINE.json configs
+WORKLOADS = {
+    "c1": dict(scene="cornell", quads=None, w=64, h=64, mode=2, spp=1,
+               name="C1 Cornell-style box 36 tris, 64x64, primary+shadow+1 bounce, 1 spp"),
+    "c2": dict(scene="terrain", quads=(250, 200), w=1024, h=1024, mode=0, spp=1,
+               name="C2 100K-tri displaced grid, 1024x1024 primary rays"),
+    "c3": dict(scene="terrain", quads=(1000, 500), w=1920, h=1080, mode=2, spp=1,
+               name="C3 1M-tri displaced grid, 1920x1080 primary+shadow+1-bounce diffuse, 1 spp"),
+    "c4": dict(scene="terrain", quads=(2500, 2000), w=3840, h=2160, mode=2, spp=8,
+               name="C4 10M-tri displaced grid, 3840x2160 x 8 spp, primary+shadow+1-bounce"),
+    "c5": dict(scene="terrain", quads=(2500, 2000), rays=64 << 20, mode=3,
+               name="C5 64Mi incoherent rays vs 10M-tri BVH, closest hit"),
+}
+ROWS_PER_BLOCK = 8  # multi-GPU row interleave granularity
+L2_FLUSH_BYTES = 256 << 20
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons while the timed region runs (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                 str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._pump, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        busy = sorted(sm)[len(sm) // 2:] if sm else []  # upper half = samples under load
+        return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def build_scene(wl, rt):
+    if wl["scene"] == "cornell":
+        soup = rt.scene_cornell()
+    else:
+        soup = rt.scene_terrain(*wl["quads"])
+    t0 = time.perf_counter()
+    nodes, tris = rt.build_bvh2(soup)
+    return soup, nodes, tris, time.perf_counter() - t0
+
+
+def scene_box(soup):
+    lo = np.minimum.reduce([soup["v0"].min(0), soup["v1"].min(0), soup["v2"].min(0)])
+    hi = np.maximum.reduce([soup["v0"].max(0), soup["v1"].max(0), soup["v2"].max(0)])
+    return lo.astype(np.float32), hi.astype(np.float32)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle on the host cores, on a bounded sample of the workload
+# ------------------------------------------------------------------------------------------------
+def cpu_sample_run(wl, soup, nodes, tris, steps, warmup):
+    """Times the CPU oracle.  Sample = the rows a rank would own if the frame were split over
+    `div` ranks (interleaved blocks of 8 rows => representative of the whole frame), or the first
+    1/div of the ray list for c5.  Returns (Mrays/s, description, threads, seconds per step)."""
+    import _oracle as o
+    threads = os.cpu_count() or 1
+    if wl["mode"] == 3:
+        n = min(wl["rays"], 1 << 20)
+        lo, hi = scene_box(soup)
+        rays = o.rays_random(lo, hi, 0x5EED5EED, 0, n)
+
+        def run():
+            _, c = o.trace(rays, nodes, tris, threads=threads, num_tasks=threads * 16)
+            return c
+        sample = f"first {n} of {wl['rays']} rays"
+    else:
+        paths = wl["w"] * wl["h"] * wl["spp"]
+        div = 1
+        while paths // div > 300_000 and div < 64:
+            div *= 2
+        a = o.make_arg(wl["w"], wl["h"], wl["mode"], spp=wl["spp"], seed=1234, scene=wl["scene"],
+                       num_tasks=wl["h"])
+        a.num_ranks, a.rank_id, a.rows_per_block = div, 0, ROWS_PER_BLOCK
+
+        def run():
+            _, c = o.render(a, nodes, tris, threads=threads)
+            return c
+        sample = (f"rows of rank 0 of {div} (interleaved blocks of {ROWS_PER_BLOCK} rows) of the "
+                  f"{wl['w']}x{wl['h']}x{wl['spp']}spp frame" if div > 1 else "the whole frame")
+    for _ in range(warmup):
+        run()
+    t0 = time.perf_counter()
+    rays_total = 0
+    for _ in range(steps):
+        c = run()
+        rays_total += c["rays_primary"] + c["rays_shadow"] + c["rays_bounce"]
+    dt = time.perf_counter() - t0
+    return rays_total / dt / 1e6, sample, threads, dt / steps, c
+
+
+def reference_arm(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from skybox_rt_b200 import raytrace as rt  # host pre-pass only (plain C, no CUDA)
+    soup, nodes, tris, _ = build_scene(wl, rt)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    v, sample, threads, sec, _ = cpu_sample_run(wl, soup, nodes, tris, steps, warmup)
+    print(json.dumps({
+        "impl": "reference", "metric": "Mrays/s (primary+shadow+bounce rays traced)", "value": v, "unit": "Mrays/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"]},
+        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference repo has no RT path (SURVEY.md section 0); this is the repo's plain-C oracle",
+    }))
+
+
+# ------------------------------------------------------------------------------------------------
+# native arm
+# ------------------------------------------------------------------------------------------------
+class DevMem:
+    """A vx buffer's device memory exposed to torch (zero copy) via __cuda_array_interface__."""
+
+    def __init__(self, address, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<u4", "data": (address, False),
+                                         "version": 2, "strides": None}
+
+
+def native_arm(args, wl):
+    import torch
+    import torch.distributed as dist
+
+    from skybox_rt_b200 import raytrace as rt
+    from skybox_rt_b200 import vortex as vx
+    from skybox_rt_b200.formats import HIT, RAY, rank_rows
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ["VX_CUDA_DEVICE"] = str(local)
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torch.distributed.run)"
+
+    soup, nodes, tris, build_s = build_scene(wl, rt)
+    tracer = rt.RayTracer(nodes, tris)
+    dev = tracer.dev
+    dev.dcr_write(vx.VX_DCR_RT_VARIANT, args.variant)
+    stream = torch.cuda.ExternalStream(dev.cuda_stream(), device=torch.device("cuda", local))
+    flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.int32, device="cuda")
+    launches = 0
+
+    rays_mode = wl["mode"] == 3
+    if rays_mode:
+        n_total = wl["rays"]
+        n_local = n_total // world
+        first = rank * n_local
+        lo, hi = scene_box(soup)
+        host_rays = torch.empty(n_local * RAY.itemsize, dtype=torch.uint8).pin_memory()
+        rt.rays_random(lo, hi, 0x5EED5EED, first, n_local, out=host_rays.numpy().view(RAY))
+        host_hits = torch.empty(n_local * HIT.itemsize, dtype=torch.uint8).pin_memory()
+        ray_buf = dev.alloc(n_local * RAY.itemsize, vx.VX_MEM_READ)
+        hit_buf = dev.alloc(n_local * HIT.itemsize)
+        ray_buf.write(host_rays)
+        from skybox_rt_b200.formats import KernelArg
+        arg = KernelArg()
+        arg.num_tasks, arg.mode = 1, 3
+        arg.ray_addr, arg.hit_addr, arg.num_rays = ray_buf.address, hit_buf.address, n_local
+        arg.node_addr, arg.tri_addr = tracer.node_buf.address, tracer.tri_buf.address
+        arg.num_nodes, arg.num_tris = tracer.num_nodes, tracer.num_tris
+        args_buf = dev.upload(arg)
+        tracer.args = args_buf
+        h2d, d2h = n_local * RAY.itemsize + 192, n_local * HIT.itemsize
+
+        def launch():
+            dev.start(tracer.kernel, args_buf)
+
+        def e2e_step(i):
+            ray_buf.write(host_rays)
+            args_buf.write(arg)
+            dev.start(tracer.kernel, args_buf)
+            dev.ready_wait()
+            hit_buf.read(host_hits)
+        gather = None
+    else:
+        W, H = wl["w"], wl["h"]
+        arg = rt.make_arg(W, H, wl["mode"], spp=wl["spp"], seed=1234, scene=wl["scene"], rank=rank,
+                          num_ranks=world, rows_per_block=ROWS_PER_BLOCK)
+        rows = tracer.start(arg)  # binds cbuf + args, first (cold) frame
+        dev.ready_wait()
+        strip = torch.as_tensor(DevMem(tracer.cbuf.address, rows * W * 4), device="cuda")
+        max_rows = max(rank_rows(H, ROWS_PER_BLOCK, world, r) for r in range(world))
+        host_frame = torch.empty(H * W, dtype=torch.int32).pin_memory()
+        h2d, d2h = 192, (H * W * 4 if rank == 0 else 0)
+        if world > 1:
+            # one NCCL gather of the strips per frame, on the render stream
+            send = torch.zeros(max_rows * W, dtype=torch.int32, device="cuda")
+            recv = [torch.empty(max_rows * W, dtype=torch.int32, device="cuda") for _ in range(world)] \
+                if rank == 0 else None
+            from skybox_rt_b200.formats import rank_row_index
+            row_idx = [torch.as_tensor(rank_row_index(H, ROWS_PER_BLOCK, world, r), device="cuda")
+                       for r in range(world)] if rank == 0 else None
+            frame_dev = torch.empty((H, W), dtype=torch.int32, device="cuda") if rank == 0 else None
+
+            def gather():
+                send[:rows * W].copy_(strip.view(torch.int32), non_blocking=True)
+                dist.gather(send, recv, dst=0)
+        else:
+            gather = None
+
+        def launch():
+            dev.start(tracer.kernel, tracer.args)
+
+        def e2e_step(i):
+            arg.seed = 1234 + i  # a new kernel_arg_t every frame, from the host
+            tracer.args.write(arg)
+            dev.start(tracer.kernel, tracer.args)
+            if gather:
+                with torch.cuda.stream(stream):
+                    gather()
+                    if rank == 0:  # de-interleave the strips on the device, one D2H copy of the frame
+                        for r in range(world):
+                            n = len(row_idx[r])
+                            frame_dev.index_copy_(0, row_idx[r], recv[r][:n * W].view(n, W))
+                        host_frame.copy_(frame_dev.view(-1), non_blocking=True)
+                stream.synchronize()
+            else:
+                dev.ready_wait()
+                tracer.cbuf.read(host_frame)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_rays():
+        c = tracer.counters()
+        return c["rays_primary"] + c["rays_shadow"] + c["rays_bounce"], c
+
+    # ---- warm-up --------------------------------------------------------------------------
+    with torch.cuda.stream(stream):
+        for _ in range(max(args.warmup, 3)):
+            launch()
+            if gather:
+                gather()
+    barrier()
+    rays_per_step, ctr = step_rays()
+
+    # ---- timed: K steps, device time on the launch stream, L2 flushed before each ------------
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    t_wall = time.perf_counter()
+    with torch.cuda.stream(stream):
+        for a, b in ev:
+            if not args.no_flush:
+                flush.zero_()
+            a.record(stream)
+            launch()
+            if gather:
+                gather()
+            b.record(stream)
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    clocks = sampler.stop()
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    kern_ns = dev.mpm_query(vx.VX_CSR_RT_ELAPSED_NS)  # vx_start..end of the last step, without gather
+
+    # ---- e2e: host buffers, copies inside the timed region, wall clock ---------------------------
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(i)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    t = torch.tensor([dev_ms, e2e_s, float(rays_per_step), kern_ns * 1e-6], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = t.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = t.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        dev_ms, e2e_s, kern_ms = mx[0].item(), mx[1].item(), mx[3].item()
+        rays_total = sm[2].item()
+    else:
+        rays_total, kern_ms = float(rays_per_step), kern_ns * 1e-6
+    return dict(rank=rank, world=world, dev_ms=dev_ms, e2e_s=e2e_s, rays_total=rays_total, kern_ms=kern_ms,
+                clocks=clocks, h2d=h2d, d2h=d2h, ctr=ctr, build_s=build_s, t_wall=t_wall, soup=soup, nodes=nodes,
+                tris=tris, tracer=tracer, n_nodes=len(nodes), n_tris=len(tris))
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def main():
+    args = parse()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        reference_arm(args, wl)
+        return
+    from skybox_rt_b200 import vortex as vx
+    r = native_arm(args, wl)
+    tracer, dev = r["tracer"], r["tracer"].dev
+    out = None
+    if r["rank"] == 0:
+        K = args.steps
+        ms_per_step = r["dev_ms"] / K
+        value = r["rays_total"] / (ms_per_step * 1e-3) / 1e6
+        e2e = r["rays_total"] / (r["e2e_s"] / K) / 1e6
+        peak, peak_src = load_peaks()
+        # algorithmic bytes of the traversal: nodes fetched x node size + triangles tested x 48 B
+        # (counted by the kernels themselves in an extra, untimed step with VX_DCR_RT_STATS = 1)
+        dev.dcr_write(vx.VX_DCR_RT_STATS, 1)
+        dev.start(tracer.kernel, tracer.args)
+        dev.ready_wait()
+        st = tracer.counters()
+        dev.dcr_write(vx.VX_DCR_RT_STATS, 0)
+        node_bytes = dev.mpm_query(vx.VX_CSR_RT_NODE_BYTES)
+        fb_bytes = 0 if wl["mode"] == 3 else wl["w"] * wl["h"] * 4 // r["world"]
+        ray_io = (r["rays_total"] / r["world"]) * 48 if wl["mode"] == 3 else 0
+        alg_bytes = st["nodes"] * node_bytes + st["tris"] * 48 + fb_bytes + ray_io
+        achieved = alg_bytes / (r["kern_ms"] * 1e-3) / 1e9 if r["kern_ms"] > 0 else 0.0
+        out = {
+            "metric": "Mrays/s (primary+shadow+bounce rays traced)", "value": value, "unit": "Mrays/s",
+            "n_gpus": r["world"], "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": wl["name"], "triangles": r["n_tris"], "bvh2_nodes": r["n_nodes"],
+                       "rays_per_step": int(r["rays_total"]), "kernel_variant": args.variant,
+                       "l2": "kept warm (--no-flush)" if args.no_flush else "flushed before every timed step (256 MiB memset)",
+                       "partition": f"rows interleaved in blocks of {ROWS_PER_BLOCK} over {r['world']} GPU(s), "
+                                    "BVH replicated, one NCCL gather per frame" if r["world"] > 1 else "single GPU"},
+            "rays": {k: r["ctr"][k] for k in ("rays_primary", "rays_shadow", "rays_bounce")},
+            "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                    "ms_per_step": r["e2e_s"] / K * 1e3},
+            "gpu_launches": int(dev.mpm_query(vx.VX_CSR_RT_LAUNCHES)) * K,
+            "clocks": r["clocks"],
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "whole vx_start pipeline (trace + shade)", "kernel_ms": r["kern_ms"],
+                         "algorithmic_bytes": int(alg_bytes), "nodes_fetched": st["nodes"],
+                         "node_bytes": int(node_bytes), "tris_tested": st["tris"]},
+            "host_prepass_s": {"bvh2_build": r["build_s"]},
+        }
+        if r["world"] == 1 and not args.no_cpu_baseline:
+            v, sample, threads, _, _ = cpu_sample_run(wl, r["soup"], r["nodes"], r["tris"], steps=3, warmup=1)
+            out["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample}
+    tracer.close()
+    if r["world"] > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    if out is not None:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -169,6 +169,8 @@ typedef struct {
 #define VX_CSR_RT_NODES        0x7C3 /* wide nodes fetched   (only when SRT_STATS is on)     */
 #define VX_CSR_RT_TRIS         0x7C4 /* triangles tested     (only when SRT_STATS is on)     */
 #define VX_CSR_RT_ELAPSED_NS   0x7C5 /* device time of the last run, CUDA events             */
+#define VX_CSR_RT_NODE_BYTES   0x7C6 /* bytes per node fetch of the kernel variant that ran  */
+#define VX_CSR_RT_LAUNCHES     0x7C7 /* kernels launched by the last vx_start                */
 
 /* ------------------------------------------------------------------------------------
  * Host builder (libskybox_rt_host: plain C, no CUDA) -- the pre-pass that plays the role

@@ -1,0 +1,28 @@
+/*
+ * vortex_cuda.h -- CUDA-specific additions to the vx_* C ABI (no counterpart in the reference).
+ *
+ * The reference host API (runtime/include/vortex.h) has no notion of a device-side queue that a
+ * second library could share.  On B200 the framebuffer gather between GPUs (NCCL) and device-side
+ * timing (CUDA events) must be ordered with the kernels vx_start enqueues, so the back-end exposes
+ * its launch stream.  Plain C: the stream is passed as void* (a cudaStream_t).
+ */
+#ifndef SKYBOX_RT_B200_VORTEX_CUDA_H
+#define SKYBOX_RT_B200_VORTEX_CUDA_H
+
+#include "vortex.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* The CUDA stream vx_start launches on and vx_copy_* are ordered with (owned by the device). */
+int vx_cuda_stream(vx_device_h hdevice, void** stream);
+
+/* CUDA device ordinal the handle was opened on. */
+int vx_cuda_device(vx_device_h hdevice, int* ordinal);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

@@ -169,9 +169,13 @@ int ort_intersect_tri(const srt_tri_rec_t* tr, v3 o, v3 d, float* t, float* u, f
 }
 
 /* ---------------------------------------------------------------- ray / box --------
- * Conservative slab test.  Zero direction components are replaced by +-1e-20 so no
- * NaN can appear; the exit distance is widened by ORT_PAD so that rounding in the slab
- * arithmetic can never cull a box whose triangle the Moeller-Trumbore test accepts. */
+ * Conservative slab test: it may only cull boxes that contain no triangle the
+ * Moeller-Trumbore test would accept, so that the traversal result equals the brute-force
+ * minimum over all triangles.  Three safeguards:
+ *   - zero direction components are replaced by +-1e-20, so no NaN can appear;
+ *   - every box is inflated by `delta` = 2^-18 * (largest |coordinate| of the root box): rays
+ *     that run exactly in a face plane of an axis-aligned box (or a hair outside it) stay inside;
+ *   - the exit distance is widened by ORT_PAD = 1 + 2^-13 against rounding in the slab products. */
 static inline float safe_inv(float d) {
   float a = d < 0.0f ? -d : d;
   float dd = a < 1e-20f ? (d < 0.0f ? -1e-20f : 1e-20f) : d;
@@ -181,10 +185,22 @@ static inline float safe_inv(float d) {
 static inline float fmin2(float a, float b) { return a < b ? a : b; }
 static inline float fmax2(float a, float b) { return a > b ? a : b; }
 
-static inline int slab(const srt_bvh2_node_t* n, v3 o, v3 id, float tmin, float tmax, float* tnear) {
-  float x0 = (n->bmin[0] - o.x) * id.x, x1 = (n->bmax[0] - o.x) * id.x;
-  float y0 = (n->bmin[1] - o.y) * id.y, y1 = (n->bmax[1] - o.y) * id.y;
-  float z0 = (n->bmin[2] - o.z) * id.z, z1 = (n->bmax[2] - o.z) * id.z;
+static inline float scene_delta(const srt_bvh2_node_t* root) {
+  float m = 0.0f;
+  int k;
+  for (k = 0; k < 3; ++k) {
+    float a = root->bmin[k] < 0.0f ? -root->bmin[k] : root->bmin[k];
+    float b = root->bmax[k] < 0.0f ? -root->bmax[k] : root->bmax[k];
+    if (a > m) m = a;
+    if (b > m) m = b;
+  }
+  return m * (1.0f / 262144.0f);
+}
+
+static inline int slab(const srt_bvh2_node_t* n, float dl, v3 o, v3 id, float tmin, float tmax, float* tnear) {
+  float x0 = ((n->bmin[0] - dl) - o.x) * id.x, x1 = ((n->bmax[0] + dl) - o.x) * id.x;
+  float y0 = ((n->bmin[1] - dl) - o.y) * id.y, y1 = ((n->bmax[1] + dl) - o.y) * id.y;
+  float z0 = ((n->bmin[2] - dl) - o.z) * id.z, z1 = ((n->bmax[2] + dl) - o.z) * id.z;
   float tn = fmax2(fmax2(fmin2(x0, x1), fmin2(y0, y1)), fmax2(fmin2(z0, z1), tmin));
   float tf = fmin2(fmin2(fmax2(x0, x1), fmax2(y0, y1)), fmin2(fmax2(z0, z1), tmax));
   *tnear = tn;
@@ -209,10 +225,10 @@ void ort_closest_hit(const srt_bvh2_node_t* nodes, const srt_tri_rec_t* tris, co
   v3 o = vload(ray->o), d = vload(ray->d);
   v3 id = V(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
   srt_hit_t best;
-  float tn;
+  float tn, dl = scene_delta(nodes);
   uint64_t nv = 1, tt = 0;
   best.t = ray->tmax; best.u = 0.0f; best.v = 0.0f; best.prim_id = SRT_MISS;
-  if (slab(nodes, o, id, ray->tmin, best.t, &tn)) { stack[0] = 0; stack_t[0] = tn; sp = 1; }
+  if (slab(nodes, dl, o, id, ray->tmin, best.t, &tn)) { stack[0] = 0; stack_t[0] = tn; sp = 1; }
   while (sp > 0) {
     const srt_bvh2_node_t* n;
     --sp;
@@ -225,8 +241,8 @@ void ort_closest_hit(const srt_bvh2_node_t* nodes, const srt_tri_rec_t* tris, co
     } else {
       float t0, t1;
       uint32_t l = n->left_first, r = l + 1;
-      int h0 = slab(nodes + l, o, id, ray->tmin, best.t, &t0);
-      int h1 = slab(nodes + r, o, id, ray->tmin, best.t, &t1);
+      int h0 = slab(nodes + l, dl, o, id, ray->tmin, best.t, &t0);
+      int h1 = slab(nodes + r, dl, o, id, ray->tmin, best.t, &t1);
       nv += 2;
       if (sp + 2 > ORT_STACK) abort();
       if (h0 && h1) { /* far child first, near child on top */
@@ -247,9 +263,9 @@ int ort_any_hit(const srt_bvh2_node_t* nodes, const srt_tri_rec_t* tris, const s
   int sp = 0, found = 0;
   v3 o = vload(ray->o), d = vload(ray->d);
   v3 id = V(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
-  float tn;
+  float tn, dl = scene_delta(nodes);
   uint64_t nv = 1, tt = 0;
-  if (slab(nodes, o, id, ray->tmin, ray->tmax, &tn)) stack[sp++] = 0;
+  if (slab(nodes, dl, o, id, ray->tmin, ray->tmax, &tn)) stack[sp++] = 0;
   while (sp > 0 && !found) {
     const srt_bvh2_node_t* n = nodes + stack[--sp];
     if (n->count > 0) {
@@ -264,8 +280,8 @@ int ort_any_hit(const srt_bvh2_node_t* nodes, const srt_tri_rec_t* tris, const s
       uint32_t l = n->left_first;
       nv += 2;
       if (sp + 2 > ORT_STACK) abort();
-      if (slab(nodes + l, o, id, ray->tmin, ray->tmax, &tn)) stack[sp++] = l;
-      if (slab(nodes + l + 1, o, id, ray->tmin, ray->tmax, &tn)) stack[sp++] = l + 1;
+      if (slab(nodes + l, dl, o, id, ray->tmin, ray->tmax, &tn)) stack[sp++] = l;
+      if (slab(nodes + l + 1, dl, o, id, ray->tmin, ray->tmax, &tn)) stack[sp++] = l + 1;
     }
   }
   if (ctr) { ctr->nodes_visited += nv; ctr->tris_tested += tt; }

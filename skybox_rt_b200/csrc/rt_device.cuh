@@ -78,6 +78,13 @@ __device__ __forceinline__ float safe_inv(float d) {
   return 1.0f / dd;
 }
 
+// Box inflation: 2^-18 * largest |coordinate| of the root box (lo/hi = root bmin/bmax).
+__device__ __forceinline__ float scene_delta(const float4 lo, const float4 hi) {
+  float m = fmaxf(fmaxf(fabsf(lo.x), fabsf(lo.y)), fabsf(lo.z));
+  m = fmaxf(m, fmaxf(fmaxf(fabsf(hi.x), fabsf(hi.y)), fabsf(hi.z)));
+  return m * (1.0f / 262144.0f);
+}
+
 struct Hit {
   float t, u, v;
   uint32_t prim;  // soup index, SRT_MISS if none
@@ -172,6 +179,18 @@ __device__ __forceinline__ V3 bounce_dir(uint32_t seed_hash, uint32_t pix, uint3
   const float bl = sqrtf(dot(bd, bd));
   if (bl < 1e-3f) bd = n; else bd = bd / bl;
   return bd;
+}
+
+// Per-thread traversal statistics -> device counters (warp reduce, one atomic per warp).  All 32
+// lanes of the warp must call this.  Counter slots: vx_internal.h CTR_NODES = 2, CTR_TRIS = 3.
+template <class S>
+__device__ __forceinline__ void flush_stats(const S& st, unsigned long long* counters) {
+  const uint32_t n = __reduce_add_sync(0xffffffffu, st.nodes);
+  const uint32_t t = __reduce_add_sync(0xffffffffu, st.tris);
+  if ((threadIdx.x & 31) == 0) {
+    if (n) atomicAdd(counters + 2, (unsigned long long)n);
+    if (t) atomicAdd(counters + 3, (unsigned long long)t);
+  }
 }
 
 // Row y of the frame -> row of this rank's strip buffer (or -1 if another rank owns it).

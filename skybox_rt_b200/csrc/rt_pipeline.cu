@@ -57,14 +57,19 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   }
   if (rt_state(dev, &st) != 0) return -1;
   cudaStream_t s = dev->stream;
+  const bool stats = dev->dcrs.count(VX_DCR_RT_STATS) && dev->dcrs[VX_DCR_RT_STATS] != 0;
+  dev->last_launches = 0;
+  dev->last_node_bytes = 32;  // baseline: one srt_bvh2_node_t per fetch
   VX_CUDA_OK(cudaMemsetAsync(st->d_counters, 0, sizeof(unsigned long long) * CTR_COUNT, s));
 
   if (a.mode == SRT_MODE_RAYS) {
     dev->last_rays_primary = a.num_rays;
     if (a.num_rays == 0) return 0;
     const uint64_t blocks = (a.num_rays + 255) / 256;
-    rt_baseline_rays_kernel<<<(unsigned)blocks, 256, 0, s>>>(a);
+    if (stats) rt_baseline_rays_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(a, st->d_counters);
+    else rt_baseline_rays_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(a, st->d_counters);
     VX_CUDA_OK(cudaGetLastError());
+    dev->last_launches = 1;
     return 0;
   }
 
@@ -73,8 +78,10 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   if (rows == 0) return 0;
   const uint32_t tiles = ((a.dst_width + 7) / 8) * ((rows + 3) / 4);  // one warp per 8x4 tile
   const uint32_t blocks = (tiles + 7) / 8;                            // 8 warps per block
-  rt_baseline_kernel<<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
+  if (stats) rt_baseline_kernel<true><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
+  else rt_baseline_kernel<false><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
   VX_CUDA_OK(cudaGetLastError());
+  dev->last_launches = 1;
   return 0;
 }
 

@@ -12,6 +12,7 @@
 
 #include <new>
 
+#include "vortex_cuda.h"
 #include "vx_internal.h"
 
 namespace srt {
@@ -99,6 +100,8 @@ int vx_dev_open(vx_device_h* hdevice) {
   dev->last_rays_primary = 0;
   dev->last_counters_valid = false;
   dev->last_pipeline = 0;
+  dev->last_launches = 0;
+  dev->last_node_bytes = 0;
   memset(dev->last_counters, 0, sizeof(dev->last_counters));
   if (cudaSetDevice(ordinal) != cudaSuccess || cudaGetDeviceProperties(&dev->prop, ordinal) != cudaSuccess ||
       cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -330,8 +333,23 @@ int vx_mpm_query(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t*
     case VX_CSR_RT_NODES: *value = c[CTR_NODES]; break;
     case VX_CSR_RT_TRIS: *value = c[CTR_TRIS]; break;
     case VX_CSR_RT_ELAPSED_NS: *value = (uint64_t)((double)ms * 1e6); break;
+    case VX_CSR_RT_NODE_BYTES: *value = dev->last_node_bytes; break;
+    case VX_CSR_RT_LAUNCHES: *value = dev->last_launches; break;
     default: return -1;
   }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------- CUDA extras
+int vx_cuda_stream(vx_device_h hdevice, void** stream) {
+  if (nullptr == hdevice || nullptr == stream) return -1;
+  *stream = (void*)as_dev(hdevice)->stream;
+  return 0;
+}
+
+int vx_cuda_device(vx_device_h hdevice, int* ordinal) {
+  if (nullptr == hdevice || nullptr == ordinal) return -1;
+  *ordinal = as_dev(hdevice)->cuda_dev;
   return 0;
 }
 

@@ -58,6 +58,8 @@ struct vx_device {
   uint64_t last_counters[CTR_COUNT];
   bool last_counters_valid;
   int last_pipeline;
+  uint32_t last_launches;       // kernels enqueued by the last vx_start
+  uint32_t last_node_bytes;     // bytes per node fetch of the kernel variant that ran
 };
 
 // DCRs owned by this back-end (outside every range the reference decodes,

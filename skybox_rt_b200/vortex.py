@@ -26,6 +26,7 @@ VX_MAX_TIMEOUT = 24 * 60 * 60 * 1000
 VX_CSR_MCYCLE, VX_CSR_MINSTRET = 0xB00, 0xB02
 VX_CSR_RT_RAYS_PRIMARY, VX_CSR_RT_RAYS_SHADOW, VX_CSR_RT_RAYS_BOUNCE = 0x7C0, 0x7C1, 0x7C2
 VX_CSR_RT_NODES, VX_CSR_RT_TRIS, VX_CSR_RT_ELAPSED_NS = 0x7C3, 0x7C4, 0x7C5
+VX_CSR_RT_NODE_BYTES, VX_CSR_RT_LAUNCHES = 0x7C6, 0x7C7
 
 # back-end DCRs (csrc/vx_internal.h)
 VX_DCR_RT_VARIANT, VX_DCR_RT_STATS = 0x800, 0x801
@@ -38,6 +39,7 @@ EXPORTS = [
     "vx_upload_kernel_file", "vx_upload_bytes", "vx_upload_file", "vx_check_occupancy", "vx_dump_perf",
     "vx_dev_init",
 ]
+CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device"]  # include/vortex_cuda.h
 
 _lib = None
 
@@ -72,6 +74,7 @@ def lib():
             "vx_upload_bytes": [vp, vp, u64, C.POINTER(vp)],
             "vx_upload_file": [vp, C.c_char_p, C.POINTER(vp)],
             "vx_check_occupancy": [vp, u32, C.POINTER(u32)],
+            "vx_cuda_stream": [vp, C.POINTER(vp)], "vx_cuda_device": [vp, C.POINTER(i)],
         }
         for name, args in sig.items():
             fn = getattr(L, name)
@@ -184,6 +187,17 @@ class Device:
         v = C.c_uint64()
         _check(lib().vx_mpm_query(self.handle, addr, core_id, C.byref(v)), "vx_mpm_query")
         return v.value
+
+    def cuda_stream(self):
+        """cudaStream_t (as int) that vx_start launches on -- wrap with torch.cuda.ExternalStream."""
+        p = C.c_void_p()
+        _check(lib().vx_cuda_stream(self.handle, C.byref(p)), "vx_cuda_stream")
+        return p.value or 0
+
+    def cuda_device(self):
+        n = C.c_int()
+        _check(lib().vx_cuda_device(self.handle, C.byref(n)), "vx_cuda_device")
+        return n.value
 
     def mem_info(self):
         f, u = C.c_uint64(), C.c_uint64()
