@@ -25,9 +25,6 @@ __device__ __forceinline__ bool slab2(const float4 lo, const float4 hi, float dl
 }
 
 // nodes as float4 pairs: [2n] = (bmin.xyz, left_first), [2n+1] = (bmax.xyz, count)
-struct Stats {
-  uint32_t nodes, tris;  // node records fetched / triangles tested by this thread
-};
 
 template <bool ANY, bool STATS>
 __device__ __forceinline__ bool bvh2_trace(const float4* __restrict__ nodes, const float4* __restrict__ tris, V3 o,

@@ -181,6 +181,10 @@ __device__ __forceinline__ V3 bounce_dir(uint32_t seed_hash, uint32_t pix, uint3
   return bd;
 }
 
+struct Stats {
+  uint32_t nodes, tris;  // node records fetched / triangles tested by this thread
+};
+
 // Per-thread traversal statistics -> device counters (warp reduce, one atomic per warp).  All 32
 // lanes of the warp must call this.  Counter slots: vx_internal.h CTR_NODES = 2, CTR_TRIS = 3.
 template <class S>

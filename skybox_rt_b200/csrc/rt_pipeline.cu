@@ -7,15 +7,34 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <vector>
+
+#include "rt_repack.h"
 #include "vx_internal.h"
 // clang-format off
 #include "rt_baseline.cuh"
+#include "rt_wide.cuh"
 // clang-format on
 
 namespace srt {
 
+// The wide-BVH image of one uploaded scene.  Built on the first vx_start that sees a given
+// (node buffer, triangle buffer) pair and reused until the app overwrites the node buffer
+// (vx_copy_to_dev bumps its generation) -- the role the tile/primitive buffers of draw3d play per
+// draw call (tests/regression/draw3d/main.cpp:190-211), except that the B200 layout is derived by
+// the back-end instead of being uploaded by the app.
+struct WideCache {
+  uint64_t node_addr, tri_addr, generation;
+  uint32_t num_nodes, num_tris;
+  float4* d_nodes4;
+  uint32_t num_nodes4, depth;
+  bool valid;
+};
+
 struct RtState {
   unsigned long long* d_counters;  // CTR_COUNT u64, zeroed at every launch
+  WideCache wide;
+  int wide_blocks_per_sm[4];       // occupancy of the persistent kernels, queried once
 };
 
 static int rt_state(vx_device* dev, RtState** out) {
@@ -29,9 +48,75 @@ static int rt_state(vx_device* dev, RtState** out) {
   return 0;
 }
 
+static vx_buffer* find_buffer(vx_device* dev, uint64_t addr) {
+  for (vx_buffer* b = dev->buffers; b; b = b->next)
+    if (addr >= b->reported_addr && addr < b->reported_addr + b->size) return b;
+  return nullptr;
+}
+
+// Make sure the Node4 image of the scene in `a` is resident; (re)build it when the scene changed.
+static int wide_prepare(vx_device* dev, RtState* st, const kernel_arg_t& a) {
+  vx_buffer* nb = find_buffer(dev, a.node_addr);
+  if (!nb || a.node_addr + (uint64_t)a.num_nodes * sizeof(srt_bvh2_node_t) > nb->reported_addr + nb->size) {
+    fprintf(stderr, "[VXDRV] raytrace: node_addr is not inside a device buffer of %u nodes\n", a.num_nodes);
+    return -1;
+  }
+  vx_buffer* tb = find_buffer(dev, a.tri_addr);
+  if (!tb || a.tri_addr + (uint64_t)a.num_tris * sizeof(srt_tri_rec_t) > tb->reported_addr + tb->size) {
+    fprintf(stderr, "[VXDRV] raytrace: tri_addr is not inside a device buffer of %u triangles\n", a.num_tris);
+    return -1;
+  }
+  WideCache& c = st->wide;
+  if (c.valid && c.node_addr == a.node_addr && c.tri_addr == a.tri_addr && c.num_nodes == a.num_nodes &&
+      c.num_tris == a.num_tris && c.generation == nb->generation)
+    return 0;
+  // read the builder's BVH2 back (the app uploaded it; the back-end keeps no host copy of large
+  // buffers) and repack it on the host: once per scene, not part of a frame
+  std::vector<srt_bvh2_node_t> n2(a.num_nodes);
+  VX_CUDA_OK(cudaMemcpyAsync(n2.data(), (const char*)nb->dptr + (a.node_addr - nb->reported_addr),
+                             n2.size() * sizeof(srt_bvh2_node_t), cudaMemcpyDeviceToHost, dev->stream));
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  std::vector<Node4> n4;
+  uint32_t depth = 0;
+  if (repack_bvh4(n2.data(), a.num_nodes, a.num_tris, n4, &depth) != 0) {
+    fprintf(stderr, "[VXDRV] raytrace: malformed BVH2 (child / triangle range out of bounds)\n");
+    return -1;
+  }
+  if (3u * depth + 1u > (uint32_t)(kSmStack + kLocalStack)) {
+    fprintf(stderr, "[VXDRV] raytrace: BVH too deep for the traversal stack (%u wide levels)\n", depth);
+    return -1;
+  }
+  if (c.d_nodes4) cudaFree(c.d_nodes4);
+  c.d_nodes4 = nullptr;
+  c.valid = false;
+  VX_CUDA_OK(cudaMalloc(&c.d_nodes4, n4.size() * sizeof(Node4)));
+  VX_CUDA_OK(cudaMemcpyAsync(c.d_nodes4, n4.data(), n4.size() * sizeof(Node4), cudaMemcpyHostToDevice, dev->stream));
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  c.node_addr = a.node_addr; c.tri_addr = a.tri_addr; c.generation = nb->generation;
+  c.num_nodes = a.num_nodes; c.num_tris = a.num_tris;
+  c.num_nodes4 = (uint32_t)n4.size(); c.depth = depth;
+  c.valid = true;
+  return 0;
+}
+
+template <class K>
+static int persistent_grid(vx_device* dev, int* cached, K kernel, size_t smem, uint64_t jobs) {
+  if (*cached == 0) {
+    int n = 0;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kWideThreads, smem) != cudaSuccess || n <= 0)
+      return -1;
+    *cached = n;
+  }
+  const uint64_t full = (uint64_t)dev->prop.multiProcessorCount * (uint64_t)*cached;
+  const uint64_t need = (jobs + kWideThreads - 1) / kWideThreads;
+  return (int)(need < full ? need : full);
+}
+
 void rt_destroy(vx_device* dev) {
   if (!dev->rt) return;
   cudaFree(dev->rt->d_counters);
+  if (dev->rt->wide.d_nodes4) cudaFree(dev->rt->wide.d_nodes4);
   delete dev->rt;
   dev->rt = nullptr;
 }
@@ -58,28 +143,74 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   if (rt_state(dev, &st) != 0) return -1;
   cudaStream_t s = dev->stream;
   const bool stats = dev->dcrs.count(VX_DCR_RT_STATS) && dev->dcrs[VX_DCR_RT_STATS] != 0;
+  const uint32_t variant = dev->dcrs.count(VX_DCR_RT_VARIANT) ? dev->dcrs[VX_DCR_RT_VARIANT] : 0u;
+  if (variant > 1u) {
+    fprintf(stderr, "[VXDRV] raytrace: unknown kernel variant %u\n", variant);
+    return -1;
+  }
+  const bool wide = variant == 0u;
   dev->last_launches = 0;
-  dev->last_node_bytes = 32;  // baseline: one srt_bvh2_node_t per fetch
+  dev->last_node_bytes = wide ? (uint32_t)sizeof(Node4) : 32u;
+  if (wide && wide_prepare(dev, st, a) != 0) return -1;
+  const WideScene sc = {st->wide.d_nodes4, reinterpret_cast<const float4*>(a.tri_addr)};
+  const size_t smem = sizeof(uint2) * kSmStack * kWideThreads;
   VX_CUDA_OK(cudaMemsetAsync(st->d_counters, 0, sizeof(unsigned long long) * CTR_COUNT, s));
 
   if (a.mode == SRT_MODE_RAYS) {
     dev->last_rays_primary = a.num_rays;
-    if (a.num_rays == 0) return 0;
-    const uint64_t blocks = (a.num_rays + 255) / 256;
-    if (stats) rt_baseline_rays_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(a, st->d_counters);
-    else rt_baseline_rays_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(a, st->d_counters);
-    VX_CUDA_OK(cudaGetLastError());
-    dev->last_launches = 1;
+    // the job cursor is 32 bits wide: long lists go out in slices of 2^30 rays
+    const uint64_t slice = 1ull << 30;
+    for (uint64_t first = 0; first < a.num_rays; first += slice) {
+      const uint64_t n = a.num_rays - first < slice ? a.num_rays - first : slice;
+      if (wide) {
+        const float4* rays = reinterpret_cast<const float4*>(a.ray_addr) + 2 * first;
+        float4* hits = reinterpret_cast<float4*>(a.hit_addr) + first;
+        if (first) VX_CUDA_OK(cudaMemsetAsync(st->d_counters + CTR_CURSOR, 0, sizeof(unsigned long long), s));
+        if (stats) {
+          const int g = persistent_grid(dev, &st->wide_blocks_per_sm[2], rt_wide_rays_kernel<true>, smem, n);
+          if (g <= 0) return -1;
+          rt_wide_rays_kernel<true><<<g, kWideThreads, smem, s>>>(rays, hits, sc, (uint32_t)n, st->d_counters);
+        } else {
+          const int g = persistent_grid(dev, &st->wide_blocks_per_sm[3], rt_wide_rays_kernel<false>, smem, n);
+          if (g <= 0) return -1;
+          rt_wide_rays_kernel<false><<<g, kWideThreads, smem, s>>>(rays, hits, sc, (uint32_t)n, st->d_counters);
+        }
+      } else {
+        kernel_arg_t b = a;
+        b.ray_addr = a.ray_addr + first * sizeof(srt_ray_t);
+        b.hit_addr = a.hit_addr + first * sizeof(srt_hit_t);
+        b.num_rays = n;
+        const uint64_t blocks = (n + 255) / 256;
+        if (stats) rt_baseline_rays_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(b, st->d_counters);
+        else rt_baseline_rays_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(b, st->d_counters);
+      }
+      VX_CUDA_OK(cudaGetLastError());
+      dev->last_launches += 1;
+    }
     return 0;
   }
 
   const uint32_t rows = srt_rank_rows(a.dst_height, a.rows_per_block, a.num_ranks, a.rank_id);
   dev->last_rays_primary = (uint64_t)rows * a.dst_width * a.spp;
   if (rows == 0) return 0;
-  const uint32_t tiles = ((a.dst_width + 7) / 8) * ((rows + 3) / 4);  // one warp per 8x4 tile
-  const uint32_t blocks = (tiles + 7) / 8;                            // 8 warps per block
-  if (stats) rt_baseline_kernel<true><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
-  else rt_baseline_kernel<false><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
+  const uint32_t tiles = ((a.dst_width + 7) / 8) * ((rows + 3) / 4);  // one 8x4 pixel tile = 32 jobs
+  if (wide) {
+    const uint64_t jobs = (uint64_t)tiles * 32u;
+    if (jobs > 0xFFFFFF00ull) return -1;
+    if (stats) {
+      const int g = persistent_grid(dev, &st->wide_blocks_per_sm[0], rt_wide_render_kernel<true>, smem, jobs);
+      if (g <= 0) return -1;
+      rt_wide_render_kernel<true><<<g, kWideThreads, smem, s>>>(a, sc, rows, (uint32_t)jobs, st->d_counters);
+    } else {
+      const int g = persistent_grid(dev, &st->wide_blocks_per_sm[1], rt_wide_render_kernel<false>, smem, jobs);
+      if (g <= 0) return -1;
+      rt_wide_render_kernel<false><<<g, kWideThreads, smem, s>>>(a, sc, rows, (uint32_t)jobs, st->d_counters);
+    }
+  } else {
+    const uint32_t blocks = (tiles + 7) / 8;  // 8 warps per block
+    if (stats) rt_baseline_kernel<true><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
+    else rt_baseline_kernel<false><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
+  }
   VX_CUDA_OK(cudaGetLastError());
   dev->last_launches = 1;
   return 0;

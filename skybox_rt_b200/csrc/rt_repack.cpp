@@ -172,4 +172,98 @@ int repack_bvh8(const srt_bvh2_node_t* n2, uint32_t num_nodes, const srt_tri_rec
   return out_tris.size() == num_tris ? 0 : -1;
 }
 
+// ------------------------------------------------------------------------------------------------
+// BVH2 -> Node4 (the layout the default traversal kernel reads, rt_wide.cuh)
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+inline float round_down(double v) {
+  float f = (float)v;
+  if ((double)f > v) f = nextafterf(f, -INFINITY);
+  return f;
+}
+inline float round_up(double v) {
+  float f = (float)v;
+  if ((double)f < v) f = nextafterf(f, INFINITY);
+  return f;
+}
+
+// children of the wide node rooted at BVH2 node `root`: open the largest internal child until 4
+int collapse4(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t root, uint32_t out[4], int& count) {
+  count = 0;
+  if (n2[root].count > 0) {  // a leaf root (tiny scene): one leaf child
+    out[count++] = root;
+    return 0;
+  }
+  float area[4];
+  auto add = [&](uint32_t n) -> int {
+    if (n >= num_nodes) return -1;
+    out[count] = n;
+    area[count++] = half_area(n2[n]);
+    return 0;
+  };
+  if (add(n2[root].left_first) || add(n2[root].left_first + 1)) return -1;
+  while (count < 4) {
+    int best = -1;
+    for (int i = 0; i < count; ++i)
+      if (n2[out[i]].count == 0 && (best < 0 || area[i] > area[best])) best = i;
+    if (best < 0) break;
+    const uint32_t l = n2[out[best]].left_first;
+    if (l + 1 >= num_nodes || l == 0) return -1;
+    out[best] = l;
+    area[best] = half_area(n2[l]);
+    if (add(l + 1)) return -1;
+  }
+  return 0;
+}
+
+}  // namespace
+
+int repack_bvh4(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t num_tris, std::vector<Node4>& out,
+                uint32_t* max_depth) {
+  if (!n2 || num_nodes == 0 || num_tris == 0 || num_tris > 0x0FFFFFFFu) return -1;
+  const double delta = (double)scene_delta_host(n2[0]);
+  out.clear();
+  out.reserve(num_nodes / 3 + 8);
+  std::vector<uint32_t> src, depth;  // BVH2 node each wide node was built from, and its level
+  src.reserve(num_nodes / 3 + 8);
+  depth.reserve(num_nodes / 3 + 8);
+  out.push_back(Node4());
+  src.push_back(0);
+  depth.push_back(1);
+  uint32_t deepest = 1;
+  for (size_t w = 0; w < out.size(); ++w) {
+    uint32_t ch[4];
+    int count;
+    if (collapse4(n2, num_nodes, src[w], ch, count) != 0) return -1;
+    Node4 nd;
+    for (int s = 0; s < 4; ++s) {
+      for (int k = 0; k < 6; ++k) nd.plane[k][s] = 3.0e38f;
+      nd.ref[s] = kEmptyRef;
+      nd.pad[s] = 0;
+    }
+    for (int s = 0; s < count; ++s) {
+      const srt_bvh2_node_t& c = n2[ch[s]];
+      for (int k = 0; k < 3; ++k) {
+        nd.plane[2 * k][s] = round_down((double)c.bmin[k] - delta);
+        nd.plane[2 * k + 1][s] = round_up((double)c.bmax[k] + delta);
+      }
+      if (c.count > 0) {
+        if (c.count > 8 || (uint64_t)c.left_first + c.count > num_tris) return -1;
+        nd.ref[s] = kLeafBit | ((c.count - 1) << 28) | c.left_first;
+      } else {
+        if (out.size() >= num_nodes) return -1;  // more wide nodes than BVH2 nodes: the input has a cycle
+        nd.ref[s] = (uint32_t)out.size();
+        out.push_back(Node4());
+        src.push_back(ch[s]);
+        depth.push_back(depth[w] + 1);
+        if (depth[w] + 1 > deepest) deepest = depth[w] + 1;
+      }
+    }
+    out[w] = nd;
+  }
+  if (max_depth) *max_depth = deepest;
+  return 0;
+}
+
 }  // namespace srt

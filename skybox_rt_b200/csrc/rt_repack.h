@@ -21,7 +21,28 @@ struct Node8 {
 };
 static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
 
+// 128 bytes = 8 x float4 = one cache line: a 4-wide node with full-precision child boxes in SoA
+// planes, so that one 16-byte load brings the same plane of all four children.
+//   q[0] = lo.x[4]  q[1] = hi.x[4]  q[2] = lo.y[4]  q[3] = hi.y[4]  q[4] = lo.z[4]  q[5] = hi.z[4]
+//   q[6] = child refs[4] (as raw bits)   q[7] = unused
+// Child ref: bit 31 clear = index of an inner Node4; bit 31 set = leaf, bits 28-30 = count-1,
+// bits 0-27 = first triangle record (in the builder's own, unpermuted record array).
+// Empty slots hold the degenerate box lo = hi = +3e38 that no ray interval can reach.
+struct Node4 {
+  float plane[6][4];
+  uint32_t ref[4];
+  uint32_t pad[4];
+};
+static_assert(sizeof(Node4) == 128, "Node4 must be 128 bytes");
+constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kEmptyRef = 0xFFFFFFFFu;
+
 float scene_delta_host(const srt_bvh2_node_t& root);
+
+// BVH2 -> Node4.  Triangle records are NOT permuted: leaves index the caller's record array.
+// max_depth = number of Node4 levels (root = 1).  Returns 0 on success.
+int repack_bvh4(const srt_bvh2_node_t* nodes2, uint32_t num_nodes, uint32_t num_tris, std::vector<Node4>& out_nodes,
+                uint32_t* max_depth);
 
 // Returns 0 on success.  out_tris is a permutation of tris.
 int repack_bvh8(const srt_bvh2_node_t* nodes2, uint32_t num_nodes, const srt_tri_rec_t* tris, uint32_t num_tris,

@@ -1,0 +1,389 @@
+// rt_wide.cuh -- variant 0, the default kernels of the RT path.
+//
+// One persistent kernel per vx_start.  Design (DESIGN.md "Kernels"):
+//   * persistent warps: grid = #SM x resident CTAs; warps pull chunks of 32 jobs (pixels, or rays
+//     of an explicit list) from one global atomic cursor, so no warp ever waits for a tail CTA;
+//   * every lane is a small state machine (primary -> shadow -> bounce -> bounce shadow) around ONE
+//     generic traversal loop: closest-hit and any-hit rays of different path stages share the same
+//     instructions, so a warp stays busy although its lanes are at different stages;
+//   * lanes whose ray has ended wait until fewer than kKeepActive lanes are still traversing; then
+//     the warp leaves the loop, the finished lanes advance their path (or take a fresh job by
+//     ballot/prefix-popc from the warp's chunk) and everybody re-enters.  This is the compaction /
+//     refill that keeps warp execution efficiency up on divergent paths;
+//   * 4-wide nodes (rt_repack.h Node4): one 128-byte line per node, fetched as seven 16-byte
+//     read-only loads; the ray octant picks the near/far plane by address, so a child costs six
+//     FMAs and two 3-input min/max;
+//   * traversal stack: the first kSmStack entries per thread live in shared memory
+//     ([entry][thread], conflict-free), deeper entries spill to a local array.
+// The ray/triangle test and all shading arithmetic are the shared, no-FMA functions of
+// rt_device.cuh; the box test uses FMA on purpose (it is conservative and never reaches an output).
+#pragma once
+
+#include "rt_device.cuh"
+
+namespace srt {
+
+constexpr int kWideThreads = 256;
+constexpr int kSmStack = 16;     // shared-memory stack entries per thread
+constexpr int kLocalStack = 80;  // spill entries per thread (local memory)
+constexpr int kKeepActive = 20;  // leave the traversal loop when fewer lanes than this are busy
+constexpr uint32_t kIdle = 0xFFFFFFFFu;
+constexpr uint32_t kChunk = 32;  // jobs per atomic fetch
+
+struct WideScene {
+  const float4* nodes;  // Node4 array, 8 float4 each
+  const float4* tris;   // srt_tri_rec_t array, 3 float4 each
+};
+
+enum { ST_PRIMARY = 0, ST_SHADOW1 = 1, ST_BOUNCE = 2, ST_SHADOW2 = 3 };
+
+struct RayState {
+  V3 o, d, idir, ood;
+  float tmin;
+  uint32_t ox, oy, oz;  // float4 index of the near plane per axis within a node: {0,1} {2,3} {4,5}
+  bool any;             // any-hit ray: stop at the first accepted triangle
+  bool found;           // any-hit result
+};
+
+__device__ __forceinline__ void ray_setup(RayState& r, V3 o, V3 d, float tmin, bool any) {
+  r.o = o;
+  r.d = d;
+  r.idir = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
+  r.ood = mk(o.x * r.idir.x, o.y * r.idir.y, o.z * r.idir.z);
+  r.tmin = tmin;
+  r.ox = r.idir.x < 0.0f ? 1u : 0u;
+  r.oy = r.idir.y < 0.0f ? 3u : 2u;
+  r.oz = r.idir.z < 0.0f ? 5u : 4u;
+  r.any = any;
+  r.found = false;
+}
+
+// One traversal stack per thread: shared entries first, local spill above.
+struct Stack {
+  uint2* sm;  // &s_stack[threadIdx.x]; entry i at sm[i * kWideThreads]
+  uint2 spill[kLocalStack];
+  int sp;
+  __device__ __forceinline__ void push(uint32_t ref, float tn) {
+    const uint2 e = make_uint2(ref, __float_as_uint(tn));
+    if (sp < kSmStack) sm[sp * kWideThreads] = e;
+    else if (sp < kSmStack + kLocalStack) spill[sp - kSmStack] = e;
+    else __trap();  // the host checked 3 * depth <= capacity before launching
+    ++sp;
+  }
+  __device__ __forceinline__ uint2 pop() {
+    --sp;
+    return sp < kSmStack ? sm[sp * kWideThreads] : spill[sp - kSmStack];
+  }
+};
+
+// Pop until an entry survives the current closest distance; kIdle when the stack is empty.
+__device__ __forceinline__ uint32_t pop_next(Stack& st, const RayState& r, float best_t) {
+  while (st.sp > 0) {
+    const uint2 e = st.pop();
+    if (__uint_as_float(e.y) <= best_t * kPad) return e.x;
+  }
+  return kIdle;
+}
+
+// ---- one inner node: test the four children, continue with the nearest, push the others --------
+// Box test per child: entry = max(near planes, tmin), exit = min(far planes, best_t); the child
+// is visited when entry <= exit * kPad.  Boxes were inflated by the scene delta at repack time.
+template <bool STATS>
+__device__ __forceinline__ uint32_t inner_step(const WideScene& sc, uint32_t cur, const RayState& r, float best_t,
+                                               Stack& st, Stats& stats) {
+  const float4* np = sc.nodes + (size_t)cur * 8;
+  const float4 nx = __ldg(np + r.ox), fx = __ldg(np + (r.ox ^ 1u));
+  const float4 ny = __ldg(np + r.oy), fy = __ldg(np + (r.oy ^ 1u));
+  const float4 nz = __ldg(np + r.oz), fz = __ldg(np + (r.oz ^ 1u));
+  const float4 rf = __ldg(np + 6);
+  if (STATS) stats.nodes += 1;
+  const float lim = best_t;
+#define SRT_CHILD(c, tn, hit)                                                                              \
+  const float tn = fmaxf(fmaxf(__fmaf_rn(nx.c, r.idir.x, -r.ood.x), __fmaf_rn(ny.c, r.idir.y, -r.ood.y)), \
+                         fmaxf(__fmaf_rn(nz.c, r.idir.z, -r.ood.z), r.tmin));                             \
+  const bool hit = tn <= fminf(fminf(__fmaf_rn(fx.c, r.idir.x, -r.ood.x), __fmaf_rn(fy.c, r.idir.y, -r.ood.y)), \
+                               fminf(__fmaf_rn(fz.c, r.idir.z, -r.ood.z), lim)) * kPad;
+  SRT_CHILD(x, t0, h0)
+  SRT_CHILD(y, t1, h1)
+  SRT_CHILD(z, t2, h2)
+  SRT_CHILD(w, t3, h3)
+#undef SRT_CHILD
+  // nearest hit child becomes the next node; the other hit children are pushed with their entry
+  // distance (checked again against the then-current closest distance when popped)
+  const float inf = __int_as_float(0x7f800000);
+  const float k0 = h0 ? t0 : inf, k1 = h1 ? t1 : inf, k2 = h2 ? t2 : inf, k3 = h3 ? t3 : inf;
+  const float kmin = fminf(fminf(k0, k1), fminf(k2, k3));
+  if (!(h0 | h1 | h2 | h3)) return pop_next(st, r, best_t);
+  uint32_t next;
+  int sel;
+  if (k0 == kmin) { sel = 0; next = __float_as_uint(rf.x); }
+  else if (k1 == kmin) { sel = 1; next = __float_as_uint(rf.y); }
+  else if (k2 == kmin) { sel = 2; next = __float_as_uint(rf.z); }
+  else { sel = 3; next = __float_as_uint(rf.w); }
+  if (h3 && sel != 3) st.push(__float_as_uint(rf.w), t3);
+  if (h2 && sel != 2) st.push(__float_as_uint(rf.z), t2);
+  if (h1 && sel != 1) st.push(__float_as_uint(rf.y), t1);
+  if (h0 && sel != 0) st.push(__float_as_uint(rf.x), t0);
+  return next;
+}
+
+// ---- one leaf: up to eight triangles --------------------------------------------------------------
+template <bool STATS>
+__device__ __forceinline__ void leaf_step(const WideScene& sc, uint32_t ref, RayState& r, Hit& best, Stats& stats) {
+  const uint32_t first = ref & 0x0FFFFFFFu, count = ((ref >> 28) & 7u) + 1u;
+  if (STATS) stats.tris += count;
+  if (r.any) {
+    for (uint32_t i = 0; i < count; ++i) {
+      const float4* tp = sc.tris + 3 * (size_t)(first + i);
+      const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
+      float t, u, v;
+      if (intersect_tri(r0, r1, r2, r.o, r.d, t, u, v) && t > r.tmin && t < best.t) {
+        r.found = true;
+        return;
+      }
+    }
+  } else {
+    for (uint32_t i = 0; i < count; ++i) consider(sc.tris, first + i, r.o, r.d, r.tmin, best);
+  }
+}
+
+// ---- the generic traversal loop -------------------------------------------------------------------
+// cur: node/leaf ref the lane is at, kIdle when the lane has no ray in flight.  Returns when fewer
+// than kKeepActive lanes of the warp are still traversing (all 32 lanes must call this together).
+template <bool STATS>
+__device__ __forceinline__ void traverse(const WideScene& sc, uint32_t& cur, RayState& r, Hit& best, Stack& st,
+                                         Stats& stats) {
+  for (;;) {
+    while ((int32_t)cur >= 0) cur = inner_step<STATS>(sc, cur, r, best.t, st, stats);
+    if (cur != kIdle) {
+      leaf_step<STATS>(sc, cur, r, best, stats);
+      if (r.any && r.found) { st.sp = 0; cur = kIdle; }
+      else cur = pop_next(st, r, best.t);
+    }
+    if (__popc(__ballot_sync(0xffffffffu, cur != kIdle)) < kKeepActive) return;
+  }
+}
+
+// ---- job pool: a warp-uniform window [next, end) of job ids, refilled kChunk at a time ------------
+struct Pool {
+  uint32_t next, end;  // warp-uniform
+  bool dry;            // the global cursor ran past the last job
+};
+
+// Hands one job id to every lane with want == true (kIdle-style ~0u when none is left).
+__device__ __forceinline__ uint32_t take_jobs(Pool& p, bool want, unsigned long long* cursor, uint32_t total_jobs) {
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t mask = __ballot_sync(0xffffffffu, want);
+  uint32_t job = ~0u;
+  if (mask == 0u) return job;
+  const uint32_t rank = __popc(mask & ((1u << lane) - 1u));
+  uint32_t n = __popc(mask);
+  uint32_t have = p.end - p.next;
+  if (want && rank < have) job = p.next + rank;
+  if (n <= have) {
+    p.next += n;
+    return job;
+  }
+  // window exhausted: fetch the next chunk (n - have <= 32 = kChunk, so one fetch is enough)
+  n -= have;
+  uint32_t base = 0;
+  if (!p.dry) {
+    if (lane == 0) base = (uint32_t)atomicAdd(cursor, (unsigned long long)kChunk);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= total_jobs) p.dry = true;
+  }
+  if (p.dry) {
+    p.next = p.end = 0;
+    return job;
+  }
+  p.next = base;
+  p.end = min(base + kChunk, total_jobs);
+  if (want && rank >= have) {
+    const uint32_t j = base + (rank - have);
+    if (j < p.end) job = j;
+  }
+  p.next = min(p.next + n, p.end);
+  return job;
+}
+
+// ---- render kernel: every lane carries one pixel through all samples and path stages --------------
+struct PathState {
+  uint32_t x, ly, pix;  // pixel, local (strip) row, frame pixel index (RNG key)
+  uint32_t s, stage;    // sample index, ST_*
+  V3 sum;               // radiance summed over finished samples
+  V3 n;                 // oriented normal at the primary hit (kept for the bounce direction)
+  float ndl;            // n.l at the hit whose shadow ray is in flight
+  float k1;             // direct term at the primary hit
+  uint32_t alb1, alb2;  // packed albedo at the primary / bounce hit
+};
+
+template <bool STATS>
+__global__ void __launch_bounds__(kWideThreads, 3)
+rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc, uint32_t local_rows,
+                      uint32_t total_jobs, unsigned long long* counters) {
+  extern __shared__ uint2 s_stack[];
+  Stack st;
+  st.sm = s_stack + threadIdx.x;
+  st.sp = 0;
+  const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
+  const uint32_t seed_hash = mix32(a.seed);
+  const Camera cam = make_camera(a);
+  Pool pool = {0u, 0u, false};
+  PathState ps = {};
+  RayState r;
+  Hit best;
+  Stats stats = {0u, 0u};
+  uint32_t cur = kIdle, n_shadow = 0u, n_bounce = 0u;
+  bool have_job = false;
+  best.t = 0.0f; best.u = 0.0f; best.v = 0.0f; best.prim = SRT_MISS; best.rec = 0u;
+  ray_setup(r, cam.eye, cam.fwd, 0.0f, false);
+
+  auto start_ray = [&](V3 o, V3 d, float tmax, bool any) {
+    ray_setup(r, o, d, 0.0f, any);
+    best.t = tmax; best.prim = SRT_MISS; best.rec = 0u;
+    st.sp = 0;
+    cur = 0u;  // root
+  };
+  auto start_primary = [&]() {
+    float jx = 0.5f, jy = 0.5f;
+    if (a.spp > 1) { jx = rnd01(seed_hash, ps.pix, ps.s, 0); jy = rnd01(seed_hash, ps.pix, ps.s, 1); }
+    ps.stage = ST_PRIMARY;
+    start_ray(cam.eye, camera_dir(cam, ps.x, global_row(a, ps.ly), jx, jy), kTMax, false);
+  };
+
+  for (;;) {
+    // ---- lanes whose ray has ended advance their path ----------------------------------------
+    if (have_job && cur == kIdle) {
+      V3 rad = ld3(a.sky);
+      bool sample_done = false;
+      if (ps.stage == ST_PRIMARY || ps.stage == ST_BOUNCE) {
+        const bool bounce = ps.stage == ST_BOUNCE;
+        if (best.prim == SRT_MISS) {
+          if (bounce) {  // c2 = sky
+            const V3 alb = unpack_albedo(ps.alb1), c2 = ld3(a.sky);
+            rad = alb * ps.k1;
+            rad.x = rad.x + (alb.x * 0.5f) * c2.x;
+            rad.y = rad.y + (alb.y * 0.5f) * c2.y;
+            rad.z = rad.z + (alb.z * 0.5f) * c2.z;
+          }
+          sample_done = true;
+        } else {
+          const float4 r1 = __ldg(sc.tris + 3 * (size_t)best.rec + 1), r2 = __ldg(sc.tris + 3 * (size_t)best.rec + 2);
+          const Surface sf = surface_at(a, r1, r2, r.o, r.d, best.t);
+          if (bounce) ps.alb2 = __float_as_uint(r1.w);
+          else { ps.alb1 = __float_as_uint(r1.w); ps.n = sf.n; }
+          ps.ndl = sf.ndl;
+          if (sf.ndl > 0.0f && a.mode >= SRT_MODE_SHADOW) {
+            ++n_shadow;
+            ps.stage = bounce ? ST_SHADOW2 : ST_SHADOW1;
+            start_ray(sf.po, sf.ld, sf.dist, true);
+          } else {
+            // no shadow ray: fall through to the "shadow finished, visible" transition below
+            r.o = sf.po;
+            r.found = false;
+            if (!(sf.ndl > 0.0f)) ps.ndl = 0.0f;  // k = ambient exactly (ambient + 0*1)
+            ps.stage = bounce ? ST_SHADOW2 : ST_SHADOW1;
+          }
+        }
+      }
+      if (!sample_done && cur == kIdle && (ps.stage == ST_SHADOW1 || ps.stage == ST_SHADOW2)) {
+        // direct term: ambient + n.l * visibility
+        const float k = (ps.ndl > 0.0f) ? (r.found ? a.ambient : a.ambient + ps.ndl) : a.ambient;
+        if (ps.stage == ST_SHADOW1) {
+          ps.k1 = k;
+          if (a.mode >= SRT_MODE_BOUNCE) {
+            ++n_bounce;
+            ps.stage = ST_BOUNCE;
+            start_ray(r.o, bounce_dir(seed_hash, ps.pix, ps.s, ps.n), kTMax, false);
+          } else {
+            rad = unpack_albedo(ps.alb1) * k;
+            sample_done = true;
+          }
+        } else {
+          const V3 alb = unpack_albedo(ps.alb1), c2 = unpack_albedo(ps.alb2) * k;
+          rad = alb * ps.k1;
+          rad.x = rad.x + (alb.x * 0.5f) * c2.x;
+          rad.y = rad.y + (alb.y * 0.5f) * c2.y;
+          rad.z = rad.z + (alb.z * 0.5f) * c2.z;
+          sample_done = true;
+        }
+      }
+      if (sample_done) {
+        ps.sum = ps.sum + rad;
+        if (++ps.s < a.spp) {
+          start_primary();
+        } else {
+          const V3 c = ps.sum / (float)a.spp;
+          *reinterpret_cast<uint32_t*>(a.cbuf_addr + (uint64_t)ps.x * a.cbuf_stride + (uint64_t)ps.ly * a.cbuf_pitch) =
+              pack_argb(c);
+          have_job = false;
+        }
+      }
+    }
+    // ---- lanes without a pixel take one from the warp's window (ballot + prefix popc) ---------
+    {
+      const uint32_t job = take_jobs(pool, !have_job, counters + CTR_CURSOR, total_jobs);
+      if (job != ~0u) {
+        const uint32_t tile = job >> 5, l = job & 31u;
+        ps.x = (tile % tiles_x) * 8u + (l & 7u);
+        ps.ly = (tile / tiles_x) * 4u + (l >> 3);
+        if (ps.x < W && ps.ly < local_rows) {
+          ps.pix = global_row(a, ps.ly) * W + ps.x;
+          ps.s = 0u;
+          ps.sum = mk(0.0f, 0.0f, 0.0f);
+          have_job = true;
+          start_primary();
+        }
+      }
+    }
+    if (pool.dry && !__any_sync(0xffffffffu, have_job)) break;
+    traverse<STATS>(sc, cur, r, best, st, stats);
+  }
+  n_shadow = __reduce_add_sync(0xffffffffu, n_shadow);
+  n_bounce = __reduce_add_sync(0xffffffffu, n_bounce);
+  if ((threadIdx.x & 31u) == 0u) {
+    if (n_shadow) atomicAdd(counters + CTR_RAYS_SHADOW, (unsigned long long)n_shadow);
+    if (n_bounce) atomicAdd(counters + CTR_RAYS_BOUNCE, (unsigned long long)n_bounce);
+  }
+  if (STATS) flush_stats(stats, counters);
+}
+
+// ---- explicit ray list (mode 3): job = ray index, closest hit, 16-byte hit record out -------------
+template <bool STATS>
+__global__ void __launch_bounds__(kWideThreads, 3)
+rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, const WideScene sc,
+                    uint32_t total_jobs, unsigned long long* counters) {
+  extern __shared__ uint2 s_stack[];
+  Stack st;
+  st.sm = s_stack + threadIdx.x;
+  st.sp = 0;
+  Pool pool = {0u, 0u, false};
+  RayState r;
+  Hit best;
+  Stats stats = {0u, 0u};
+  uint32_t cur = kIdle, my_ray = 0u;
+  bool have_job = false;
+  best.t = 0.0f; best.u = 0.0f; best.v = 0.0f; best.prim = SRT_MISS; best.rec = 0u;
+  ray_setup(r, mk(0.0f, 0.0f, 0.0f), mk(0.0f, 0.0f, 1.0f), 0.0f, false);
+  for (;;) {
+    if (have_job && cur == kIdle) {
+      hits[my_ray] = make_float4(best.t, best.u, best.v, __uint_as_float(best.prim));
+      have_job = false;
+    }
+    const uint32_t job = take_jobs(pool, !have_job, counters + CTR_CURSOR, total_jobs);
+    if (job != ~0u) {
+      const float4 r0 = __ldg(rays + 2 * (size_t)job), r1 = __ldg(rays + 2 * (size_t)job + 1);
+      my_ray = job;
+      have_job = true;
+      ray_setup(r, mk(r0.x, r0.y, r0.z), mk(r1.x, r1.y, r1.z), r0.w, false);
+      best.t = r1.w; best.u = 0.0f; best.v = 0.0f; best.prim = SRT_MISS; best.rec = 0u;
+      st.sp = 0;
+      cur = 0u;
+    }
+    if (pool.dry && !__any_sync(0xffffffffu, have_job)) break;
+    traverse<STATS>(sc, cur, r, best, st, stats);
+  }
+  if (STATS) flush_stats(stats, counters);
+}
+
+}  // namespace srt

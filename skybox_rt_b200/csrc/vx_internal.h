@@ -36,6 +36,7 @@ enum {
   CTR_RAYS_BOUNCE = 1,
   CTR_NODES = 2,
   CTR_TRIS = 3,
+  CTR_CURSOR = 4,  // job cursor of the persistent kernels
   CTR_COUNT = 8
 };
 
