@@ -53,6 +53,9 @@ def parse():
     ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
+    ap.add_argument("--keep-active", type=int, default=0, help="diagnostic: refill threshold DCR (0 = default)")
+    ap.add_argument("--mode", type=int, default=None, help="diagnostic: override the workload's shading mode (0/1/2)")
+    ap.add_argument("--spp", type=int, default=None, help="diagnostic: override the workload's samples per pixel")
     return ap.parse_args()
 
 
@@ -210,6 +213,7 @@ def native_arm(args, wl):
     tracer = rt.RayTracer(nodes, tris)
     dev = tracer.dev
     dev.dcr_write(vx.VX_DCR_RT_VARIANT, args.variant)
+    dev.dcr_write(vx.VX_DCR_RT_KEEP_ACTIVE, args.keep_active)
     stream = torch.cuda.ExternalStream(dev.cuda_stream(), device=torch.device("cuda", local))
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.int32, device="cuda")
     launches = 0
@@ -366,7 +370,13 @@ def load_peaks():
 
 def main():
     args = parse()
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.mode is not None and wl["mode"] != 3:
+        wl["mode"] = args.mode
+        wl["name"] += f" [diagnostic: mode {args.mode}]"
+    if args.spp is not None and wl["mode"] != 3:
+        wl["spp"] = args.spp
+        wl["name"] += f" [diagnostic: spp {args.spp}]"
     if args.impl == "reference":
         reference_arm(args, wl)
         return

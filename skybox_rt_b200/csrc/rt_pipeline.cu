@@ -152,7 +152,9 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   dev->last_launches = 0;
   dev->last_node_bytes = wide ? (uint32_t)sizeof(Node4) : 32u;
   if (wide && wide_prepare(dev, st, a) != 0) return -1;
-  const WideScene sc = {st->wide.d_nodes4, reinterpret_cast<const float4*>(a.tri_addr)};
+  uint32_t keep = dev->dcrs.count(VX_DCR_RT_KEEP_ACTIVE) ? dev->dcrs[VX_DCR_RT_KEEP_ACTIVE] : 0u;
+  if (keep == 0u || keep > 32u) keep = kKeepActive;
+  const WideScene sc = {st->wide.d_nodes4, reinterpret_cast<const float4*>(a.tri_addr), (int)keep};
   const size_t smem = sizeof(uint2) * kSmStack * kWideThreads;
   VX_CUDA_OK(cudaMemsetAsync(st->d_counters, 0, sizeof(unsigned long long) * CTR_COUNT, s));
 

@@ -26,13 +26,14 @@ namespace srt {
 constexpr int kWideThreads = 256;
 constexpr int kSmStack = 16;     // shared-memory stack entries per thread
 constexpr int kLocalStack = 80;  // spill entries per thread (local memory)
-constexpr int kKeepActive = 20;  // leave the traversal loop when fewer lanes than this are busy
+constexpr int kKeepActive = 20;  // default: leave the traversal loop when fewer lanes than this are busy
 constexpr uint32_t kIdle = 0xFFFFFFFFu;
 constexpr uint32_t kChunk = 32;  // jobs per atomic fetch
 
 struct WideScene {
   const float4* nodes;  // Node4 array, 8 float4 each
   const float4* tris;   // srt_tri_rec_t array, 3 float4 each
+  int keep_active;      // refill threshold (VX_DCR_RT_KEEP_ACTIVE, default kKeepActive)
 };
 
 enum { ST_PRIMARY = 0, ST_SHADOW1 = 1, ST_BOUNCE = 2, ST_SHADOW2 = 3 };
@@ -160,7 +161,7 @@ __device__ __forceinline__ void traverse(const WideScene& sc, uint32_t& cur, Ray
       if (r.any && r.found) { st.sp = 0; cur = kIdle; }
       else cur = pop_next(st, r, best.t);
     }
-    if (__popc(__ballot_sync(0xffffffffu, cur != kIdle)) < kKeepActive) return;
+    if (__popc(__ballot_sync(0xffffffffu, cur != kIdle)) < sc.keep_active) return;
   }
 }
 

@@ -68,6 +68,7 @@ struct vx_device {
 #define VX_DCR_RT_BASE    0x800
 #define VX_DCR_RT_VARIANT 0x800 /* 0 = default (wide BVH, wavefront), 1 = baseline BVH2 megakernel */
 #define VX_DCR_RT_STATS   0x801 /* 1 = count node fetches / triangle tests (slower)               */
+#define VX_DCR_RT_KEEP_ACTIVE 0x802 /* tuning: refill threshold of the persistent kernels (1..32), 0 = default */
 #define VX_DCR_RT_END     0x810
 
 namespace srt {

@@ -29,7 +29,7 @@ VX_CSR_RT_NODES, VX_CSR_RT_TRIS, VX_CSR_RT_ELAPSED_NS = 0x7C3, 0x7C4, 0x7C5
 VX_CSR_RT_NODE_BYTES, VX_CSR_RT_LAUNCHES = 0x7C6, 0x7C7
 
 # back-end DCRs (csrc/vx_internal.h)
-VX_DCR_RT_VARIANT, VX_DCR_RT_STATS = 0x800, 0x801
+VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE = 0x800, 0x801, 0x802
 RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE = 0, 1
 
 EXPORTS = [
