@@ -50,7 +50,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel")
+    ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel, 2 wide while-while")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
     ap.add_argument("--keep-active", type=int, default=0, help="diagnostic: refill threshold DCR (0 = default)")

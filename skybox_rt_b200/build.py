@@ -56,6 +56,17 @@ def _run(cmd, verbose):
     subprocess.run(cmd, check=True)
 
 
+def build_experiment(tag, defines, verbose=False):
+    """A/B helper: build the CUDA back-end alone with extra -D macros into lib/exp_<tag>/libvortex.so
+    (select it at run time with SKYBOX_RT_LIB=<path>).  Not part of the product build."""
+    out_dir = os.path.join(LIB, "exp_" + tag)
+    os.makedirs(out_dir, exist_ok=True)
+    cu_src = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cpp"))]
+    out = os.path.join(out_dir, "libvortex.so")
+    _run([NVCC] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-shared", "-o", out] + cu_src, verbose)
+    return out
+
+
 def build(force=False, verbose=False):
     os.makedirs(LIB, exist_ok=True)
     os.makedirs(BIN, exist_ok=True)
@@ -88,4 +99,8 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    build(force="--force" in sys.argv, verbose=True)
+    if "--exp" in sys.argv:  # python -m skybox_rt_b200.build --exp TAG -DNAME=VALUE ...
+        i = sys.argv.index("--exp")
+        build_experiment(sys.argv[i + 1], [a[2:] for a in sys.argv[i + 2:] if a.startswith("-D")], verbose=True)
+    else:
+        build(force="--force" in sys.argv, verbose=True)

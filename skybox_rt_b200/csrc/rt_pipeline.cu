@@ -34,7 +34,7 @@ struct WideCache {
 struct RtState {
   unsigned long long* d_counters;  // CTR_COUNT u64, zeroed at every launch
   WideCache wide;
-  int wide_blocks_per_sm[4];       // occupancy of the persistent kernels, queried once
+  int wide_blocks_per_sm[8];       // occupancy of the persistent kernels, queried once
 };
 
 static int rt_state(vx_device* dev, RtState** out) {
@@ -68,7 +68,7 @@ static int wide_prepare(vx_device* dev, RtState* st, const kernel_arg_t& a) {
   }
   WideCache& c = st->wide;
   if (c.valid && c.node_addr == a.node_addr && c.tri_addr == a.tri_addr && c.num_nodes == a.num_nodes &&
-      c.num_tris == a.num_tris && c.generation == nb->generation)
+      c.num_tris == a.num_tris && c.generation == nb->generation + tb->generation)
     return 0;
   // read the builder's BVH2 back (the app uploaded it; the back-end keeps no host copy of large
   // buffers) and repack it on the host: once per scene, not part of a frame
@@ -76,10 +76,15 @@ static int wide_prepare(vx_device* dev, RtState* st, const kernel_arg_t& a) {
   VX_CUDA_OK(cudaMemcpyAsync(n2.data(), (const char*)nb->dptr + (a.node_addr - nb->reported_addr),
                              n2.size() * sizeof(srt_bvh2_node_t), cudaMemcpyDeviceToHost, dev->stream));
   VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  std::vector<srt_tri_rec_t> tr(a.num_tris);
+  VX_CUDA_OK(cudaMemcpyAsync(tr.data(), (const char*)tb->dptr + (a.tri_addr - tb->reported_addr),
+                             tr.size() * sizeof(srt_tri_rec_t), cudaMemcpyDeviceToHost, dev->stream));
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
   std::vector<Node4> n4;
   uint32_t depth = 0;
-  if (repack_bvh4(n2.data(), a.num_nodes, a.num_tris, n4, &depth) != 0) {
-    fprintf(stderr, "[VXDRV] raytrace: malformed BVH2 (child / triangle range out of bounds)\n");
+  if (repack_bvh4(n2.data(), a.num_nodes, tr.data(), a.num_tris, n4, &depth) != 0) {
+    fprintf(stderr, "[VXDRV] raytrace: malformed BVH2 (child / triangle range out of bounds, or a leaf with more "
+                    "than %d triangles)\n", SRT_MAX_LEAF_TRIS);
     return -1;
   }
   if (3u * depth + 1u > (uint32_t)(kSmStack + kLocalStack)) {
@@ -92,7 +97,7 @@ static int wide_prepare(vx_device* dev, RtState* st, const kernel_arg_t& a) {
   VX_CUDA_OK(cudaMalloc(&c.d_nodes4, n4.size() * sizeof(Node4)));
   VX_CUDA_OK(cudaMemcpyAsync(c.d_nodes4, n4.data(), n4.size() * sizeof(Node4), cudaMemcpyHostToDevice, dev->stream));
   VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
-  c.node_addr = a.node_addr; c.tri_addr = a.tri_addr; c.generation = nb->generation;
+  c.node_addr = a.node_addr; c.tri_addr = a.tri_addr; c.generation = nb->generation + tb->generation;
   c.num_nodes = a.num_nodes; c.num_tris = a.num_tris;
   c.num_nodes4 = (uint32_t)n4.size(); c.depth = depth;
   c.valid = true;
@@ -144,19 +149,47 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   cudaStream_t s = dev->stream;
   const bool stats = dev->dcrs.count(VX_DCR_RT_STATS) && dev->dcrs[VX_DCR_RT_STATS] != 0;
   const uint32_t variant = dev->dcrs.count(VX_DCR_RT_VARIANT) ? dev->dcrs[VX_DCR_RT_VARIANT] : 0u;
-  if (variant > 1u) {
+  if (variant > 2u) {
     fprintf(stderr, "[VXDRV] raytrace: unknown kernel variant %u\n", variant);
     return -1;
   }
-  const bool wide = variant == 0u;
+  const bool wide = variant != 1u;
+  const int sched = variant == 2u ? SCHED_WHILE : SCHED_VOTE;
   dev->last_launches = 0;
   dev->last_node_bytes = wide ? (uint32_t)sizeof(Node4) : 32u;
   if (wide && wide_prepare(dev, st, a) != 0) return -1;
-  uint32_t keep = dev->dcrs.count(VX_DCR_RT_KEEP_ACTIVE) ? dev->dcrs[VX_DCR_RT_KEEP_ACTIVE] : 0u;
-  if (keep == 0u || keep > 32u) keep = kKeepActive;
-  const WideScene sc = {st->wide.d_nodes4, reinterpret_cast<const float4*>(a.tri_addr), (int)keep};
+  uint32_t tune = dev->dcrs.count(VX_DCR_RT_KEEP_ACTIVE) ? dev->dcrs[VX_DCR_RT_KEEP_ACTIVE] : 0u;
+  if (sched == SCHED_WHILE) {
+    if (tune == 0u || tune > 32u) tune = kKeepActive;
+  } else {
+    uint32_t ta = tune & 0xffu, tt = (tune >> 8) & 0xffu;
+    if (ta == 0u || ta > 32u) ta = kAdvanceAt;
+    if (tt == 0u || tt > 32u) tt = kTriAt;
+    tune = ta | (tt << 8);
+  }
+  const WideScene sc = {st->wide.d_nodes4, reinterpret_cast<const float4*>(a.tri_addr), (int)tune};
   const size_t smem = sizeof(uint2) * kSmStack * kWideThreads;
+  int* occ = st->wide_blocks_per_sm + (sched * 4 + (stats ? 2 : 0));
   VX_CUDA_OK(cudaMemsetAsync(st->d_counters, 0, sizeof(unsigned long long) * CTR_COUNT, s));
+
+// launch one of the four instantiations of a persistent kernel
+#define SRT_LAUNCH_WIDE(KERNEL, OCC, JOBS, ...)                                                    \
+  do {                                                                                             \
+    int g_;                                                                                        \
+    if (sched == SCHED_VOTE && stats) {                                                            \
+      if ((g_ = persistent_grid(dev, OCC, KERNEL<SCHED_VOTE, true>, smem, JOBS)) <= 0) return -1;  \
+      KERNEL<SCHED_VOTE, true><<<g_, kWideThreads, smem, s>>>(__VA_ARGS__);                        \
+    } else if (sched == SCHED_VOTE) {                                                              \
+      if ((g_ = persistent_grid(dev, OCC, KERNEL<SCHED_VOTE, false>, smem, JOBS)) <= 0) return -1; \
+      KERNEL<SCHED_VOTE, false><<<g_, kWideThreads, smem, s>>>(__VA_ARGS__);                       \
+    } else if (stats) {                                                                            \
+      if ((g_ = persistent_grid(dev, OCC, KERNEL<SCHED_WHILE, true>, smem, JOBS)) <= 0) return -1; \
+      KERNEL<SCHED_WHILE, true><<<g_, kWideThreads, smem, s>>>(__VA_ARGS__);                       \
+    } else {                                                                                       \
+      if ((g_ = persistent_grid(dev, OCC, KERNEL<SCHED_WHILE, false>, smem, JOBS)) <= 0) return -1;\
+      KERNEL<SCHED_WHILE, false><<<g_, kWideThreads, smem, s>>>(__VA_ARGS__);                      \
+    }                                                                                              \
+  } while (0)
 
   if (a.mode == SRT_MODE_RAYS) {
     dev->last_rays_primary = a.num_rays;
@@ -168,15 +201,7 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
         const float4* rays = reinterpret_cast<const float4*>(a.ray_addr) + 2 * first;
         float4* hits = reinterpret_cast<float4*>(a.hit_addr) + first;
         if (first) VX_CUDA_OK(cudaMemsetAsync(st->d_counters + CTR_CURSOR, 0, sizeof(unsigned long long), s));
-        if (stats) {
-          const int g = persistent_grid(dev, &st->wide_blocks_per_sm[2], rt_wide_rays_kernel<true>, smem, n);
-          if (g <= 0) return -1;
-          rt_wide_rays_kernel<true><<<g, kWideThreads, smem, s>>>(rays, hits, sc, (uint32_t)n, st->d_counters);
-        } else {
-          const int g = persistent_grid(dev, &st->wide_blocks_per_sm[3], rt_wide_rays_kernel<false>, smem, n);
-          if (g <= 0) return -1;
-          rt_wide_rays_kernel<false><<<g, kWideThreads, smem, s>>>(rays, hits, sc, (uint32_t)n, st->d_counters);
-        }
+        SRT_LAUNCH_WIDE(rt_wide_rays_kernel, occ + 1, n, rays, hits, sc, (uint32_t)n, st->d_counters);
       } else {
         kernel_arg_t b = a;
         b.ray_addr = a.ray_addr + first * sizeof(srt_ray_t);
@@ -199,20 +224,13 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   if (wide) {
     const uint64_t jobs = (uint64_t)tiles * 32u;
     if (jobs > 0xFFFFFF00ull) return -1;
-    if (stats) {
-      const int g = persistent_grid(dev, &st->wide_blocks_per_sm[0], rt_wide_render_kernel<true>, smem, jobs);
-      if (g <= 0) return -1;
-      rt_wide_render_kernel<true><<<g, kWideThreads, smem, s>>>(a, sc, rows, (uint32_t)jobs, st->d_counters);
-    } else {
-      const int g = persistent_grid(dev, &st->wide_blocks_per_sm[1], rt_wide_render_kernel<false>, smem, jobs);
-      if (g <= 0) return -1;
-      rt_wide_render_kernel<false><<<g, kWideThreads, smem, s>>>(a, sc, rows, (uint32_t)jobs, st->d_counters);
-    }
+    SRT_LAUNCH_WIDE(rt_wide_render_kernel, occ, jobs, a, sc, rows, (uint32_t)jobs, st->d_counters);
   } else {
     const uint32_t blocks = (tiles + 7) / 8;  // 8 warps per block
     if (stats) rt_baseline_kernel<true><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
     else rt_baseline_kernel<false><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);
   }
+#undef SRT_LAUNCH_WIDE
   VX_CUDA_OK(cudaGetLastError());
   dev->last_launches = 1;
   return 0;

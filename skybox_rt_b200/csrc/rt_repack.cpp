@@ -188,54 +188,78 @@ inline float round_up(double v) {
   return f;
 }
 
-// children of the wide node rooted at BVH2 node `root`: open the largest internal child until 4
-int collapse4(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t root, uint32_t out[4], int& count) {
+// One prospective child of a wide node: a BVH2 node (inner, or a leaf not yet opened) or one triangle.
+struct Ent {
+  uint32_t id;
+  bool tri;
+  float area;
+};
+
+// Children of the wide node built from BVH2 node `root`.  Starting from root's two children, the
+// entry with the largest surface area that still fits is opened: an inner node is replaced by its
+// two children, a leaf by its (<= 4) triangles.  Every child ends up an inner node (or a leaf that
+// did not fit and becomes a wide node of its own one level down) or a single triangle.
+int collapse4(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t num_tris, uint32_t root, Ent out[4],
+              int& count) {
   count = 0;
-  if (n2[root].count > 0) {  // a leaf root (tiny scene): one leaf child
-    out[count++] = root;
-    return 0;
-  }
-  float area[4];
-  auto add = [&](uint32_t n) -> int {
-    if (n >= num_nodes) return -1;
-    out[count] = n;
-    area[count++] = half_area(n2[n]);
+  auto add_node = [&](uint32_t n) -> int {
+    if (n >= num_nodes || n == 0) return -1;
+    if (n2[n].count > SRT_MAX_LEAF_TRIS || (uint64_t)n2[n].left_first + n2[n].count > num_tris) return -1;
+    out[count++] = Ent{n, false, half_area(n2[n])};
     return 0;
   };
-  if (add(n2[root].left_first) || add(n2[root].left_first + 1)) return -1;
-  while (count < 4) {
+  const srt_bvh2_node_t& r = n2[root];
+  if (r.count > 0) {  // the wide node is a leaf's triangle fan
+    if (r.count > SRT_MAX_LEAF_TRIS || (uint64_t)r.left_first + r.count > num_tris) return -1;
+    for (uint32_t t = 0; t < r.count; ++t) out[count++] = Ent{r.left_first + t, true, 0.0f};
+    return 0;
+  }
+  if (add_node(r.left_first) || add_node(r.left_first + 1)) return -1;
+  for (;;) {
     int best = -1;
-    for (int i = 0; i < count; ++i)
-      if (n2[out[i]].count == 0 && (best < 0 || area[i] > area[best])) best = i;
+    for (int i = 0; i < count; ++i) {
+      if (out[i].tri) continue;
+      const srt_bvh2_node_t& c = n2[out[i].id];
+      const int grow = c.count > 0 ? (int)c.count - 1 : 1;
+      if (count + grow > 4) continue;
+      if (best < 0 || out[i].area > out[best].area) best = i;
+    }
     if (best < 0) break;
-    const uint32_t l = n2[out[best]].left_first;
-    if (l + 1 >= num_nodes || l == 0) return -1;
-    out[best] = l;
-    area[best] = half_area(n2[l]);
-    if (add(l + 1)) return -1;
+    const srt_bvh2_node_t c = n2[out[best].id];
+    if (c.count > 0) {
+      out[best] = Ent{c.left_first, true, 0.0f};
+      for (uint32_t t = 1; t < c.count; ++t) out[count++] = Ent{c.left_first + t, true, 0.0f};
+    } else {
+      const uint32_t l = c.left_first;
+      if (l + 1 >= num_nodes || l == 0) return -1;
+      if (n2[l].count > SRT_MAX_LEAF_TRIS || (uint64_t)n2[l].left_first + n2[l].count > num_tris) return -1;
+      out[best] = Ent{l, false, half_area(n2[l])};
+      if (add_node(l + 1)) return -1;
+    }
   }
   return 0;
 }
 
 }  // namespace
 
-int repack_bvh4(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t num_tris, std::vector<Node4>& out,
-                uint32_t* max_depth) {
-  if (!n2 || num_nodes == 0 || num_tris == 0 || num_tris > 0x0FFFFFFFu) return -1;
+int repack_bvh4(const srt_bvh2_node_t* n2, uint32_t num_nodes, const srt_tri_rec_t* tris, uint32_t num_tris,
+                std::vector<Node4>& out, uint32_t* max_depth) {
+  if (!n2 || !tris || num_nodes == 0 || num_tris == 0 || num_tris > 0x7FFFFFFFu) return -1;
+  if (n2[0].count > SRT_MAX_LEAF_TRIS || (n2[0].count > 0 && n2[0].count > num_tris)) return -1;
   const double delta = (double)scene_delta_host(n2[0]);
   out.clear();
-  out.reserve(num_nodes / 3 + 8);
+  out.reserve(num_nodes / 2 + 8);
   std::vector<uint32_t> src, depth;  // BVH2 node each wide node was built from, and its level
-  src.reserve(num_nodes / 3 + 8);
-  depth.reserve(num_nodes / 3 + 8);
+  src.reserve(num_nodes / 2 + 8);
+  depth.reserve(num_nodes / 2 + 8);
   out.push_back(Node4());
   src.push_back(0);
   depth.push_back(1);
   uint32_t deepest = 1;
   for (size_t w = 0; w < out.size(); ++w) {
-    uint32_t ch[4];
+    Ent ch[4];
     int count;
-    if (collapse4(n2, num_nodes, src[w], ch, count) != 0) return -1;
+    if (collapse4(n2, num_nodes, num_tris, src[w], ch, count) != 0) return -1;
     Node4 nd;
     for (int s = 0; s < 4; ++s) {
       for (int k = 0; k < 6; ++k) nd.plane[k][s] = 3.0e38f;
@@ -243,21 +267,28 @@ int repack_bvh4(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t num_tris
       nd.pad[s] = 0;
     }
     for (int s = 0; s < count; ++s) {
-      const srt_bvh2_node_t& c = n2[ch[s]];
-      for (int k = 0; k < 3; ++k) {
-        nd.plane[2 * k][s] = round_down((double)c.bmin[k] - delta);
-        nd.plane[2 * k + 1][s] = round_up((double)c.bmax[k] + delta);
-      }
-      if (c.count > 0) {
-        if (c.count > 8 || (uint64_t)c.left_first + c.count > num_tris) return -1;
-        nd.ref[s] = kLeafBit | ((c.count - 1) << 28) | c.left_first;
+      double lo[3], hi[3];
+      if (ch[s].tri) {
+        const srt_tri_rec_t& t = tris[ch[s].id];
+        for (int k = 0; k < 3; ++k) {
+          const double a = (double)t.v0[k], b = a + (double)t.e1[k], c = a + (double)t.e2[k];
+          lo[k] = std::min(a, std::min(b, c));
+          hi[k] = std::max(a, std::max(b, c));
+        }
+        nd.ref[s] = kTriBit | ch[s].id;
       } else {
-        if (out.size() >= num_nodes) return -1;  // more wide nodes than BVH2 nodes: the input has a cycle
+        const srt_bvh2_node_t& c = n2[ch[s].id];
+        for (int k = 0; k < 3; ++k) { lo[k] = (double)c.bmin[k]; hi[k] = (double)c.bmax[k]; }
+        if (out.size() >= (size_t)num_nodes + 1) return -1;  // more wide nodes than BVH2 nodes: a cycle
         nd.ref[s] = (uint32_t)out.size();
         out.push_back(Node4());
-        src.push_back(ch[s]);
+        src.push_back(ch[s].id);
         depth.push_back(depth[w] + 1);
         if (depth[w] + 1 > deepest) deepest = depth[w] + 1;
+      }
+      for (int k = 0; k < 3; ++k) {
+        nd.plane[2 * k][s] = round_down(lo[k] - delta);
+        nd.plane[2 * k + 1][s] = round_up(hi[k] + delta);
       }
     }
     out[w] = nd;

@@ -25,8 +25,9 @@ static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
 // planes, so that one 16-byte load brings the same plane of all four children.
 //   q[0] = lo.x[4]  q[1] = hi.x[4]  q[2] = lo.y[4]  q[3] = hi.y[4]  q[4] = lo.z[4]  q[5] = hi.z[4]
 //   q[6] = child refs[4] (as raw bits)   q[7] = unused
-// Child ref: bit 31 clear = index of an inner Node4; bit 31 set = leaf, bits 28-30 = count-1,
-// bits 0-27 = first triangle record (in the builder's own, unpermuted record array).
+// Child ref: bit 31 clear = index of another Node4; bit 31 set = ONE triangle, bits 0-30 = its record
+// index in the builder's own, unpermuted record array (the child box is then that triangle's box, so
+// the ray/triangle test only runs for triangles whose box the ray enters).
 // Empty slots hold the degenerate box lo = hi = +3e38 that no ray interval can reach.
 struct Node4 {
   float plane[6][4];
@@ -34,15 +35,16 @@ struct Node4 {
   uint32_t pad[4];
 };
 static_assert(sizeof(Node4) == 128, "Node4 must be 128 bytes");
-constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kTriBit = 0x80000000u;
 constexpr uint32_t kEmptyRef = 0xFFFFFFFFu;
 
 float scene_delta_host(const srt_bvh2_node_t& root);
 
-// BVH2 -> Node4.  Triangle records are NOT permuted: leaves index the caller's record array.
-// max_depth = number of Node4 levels (root = 1).  Returns 0 on success.
-int repack_bvh4(const srt_bvh2_node_t* nodes2, uint32_t num_nodes, uint32_t num_tris, std::vector<Node4>& out_nodes,
-                uint32_t* max_depth);
+// BVH2 -> Node4.  Triangle records are NOT permuted: triangle refs index the caller's record array.
+// max_depth = number of Node4 levels (root = 1).  Returns 0 on success, -1 on a malformed BVH2
+// (child / triangle range out of bounds, leaf larger than SRT_MAX_LEAF_TRIS, cycle).
+int repack_bvh4(const srt_bvh2_node_t* nodes2, uint32_t num_nodes, const srt_tri_rec_t* tris, uint32_t num_tris,
+                std::vector<Node4>& out_nodes, uint32_t* max_depth);
 
 // Returns 0 on success.  out_tris is a permutation of tris.
 int repack_bvh8(const srt_bvh2_node_t* nodes2, uint32_t num_nodes, const srt_tri_rec_t* tris, uint32_t num_tris,

@@ -1,15 +1,17 @@
-// rt_wide.cuh -- variant 0, the default kernels of the RT path.
+// rt_wide.cuh -- the default kernels of the RT path.
 //
 // One persistent kernel per vx_start.  Design (DESIGN.md "Kernels"):
 //   * persistent warps: grid = #SM x resident CTAs; warps pull chunks of 32 jobs (pixels, or rays
 //     of an explicit list) from one global atomic cursor, so no warp ever waits for a tail CTA;
 //   * every lane is a small state machine (primary -> shadow -> bounce -> bounce shadow) around ONE
-//     generic traversal loop: closest-hit and any-hit rays of different path stages share the same
+//     generic traversal core: closest-hit and any-hit rays of different path stages share the same
 //     instructions, so a warp stays busy although its lanes are at different stages;
-//   * lanes whose ray has ended wait until fewer than kKeepActive lanes are still traversing; then
-//     the warp leaves the loop, the finished lanes advance their path (or take a fresh job by
-//     ballot/prefix-popc from the warp's chunk) and everybody re-enters.  This is the compaction /
-//     refill that keeps warp execution efficiency up on divergent paths;
+//   * a lane always wants exactly one of three kinds of work: a NODE step (test the four children
+//     of a wide node), a TRIANGLE step (one ray/triangle test of its pending leaf), or an ADVANCE
+//     step (its ray has ended: shade, spawn the next ray of the path, or take a new job by
+//     ballot / prefix-popc from the warp's chunk -- the compaction / refill).  Each iteration the
+//     warp votes (two ballots) and runs the step that most lanes want (SCHED_VOTE); the classic
+//     while-while loop with a refill threshold is kept as SCHED_WHILE for A/B measurements;
 //   * 4-wide nodes (rt_repack.h Node4): one 128-byte line per node, fetched as seven 16-byte
 //     read-only loads; the ray octant picks the near/far plane by address, so a child costs six
 //     FMAs and two 3-input min/max;
@@ -23,17 +25,27 @@
 
 namespace srt {
 
+#ifndef SRT_SM_STACK
+#define SRT_SM_STACK 16
+#endif
+#ifndef SRT_MIN_BLOCKS
+#define SRT_MIN_BLOCKS 3
+#endif
 constexpr int kWideThreads = 256;
-constexpr int kSmStack = 16;     // shared-memory stack entries per thread
+constexpr int kSmStack = SRT_SM_STACK;  // shared-memory stack entries per thread
 constexpr int kLocalStack = 80;  // spill entries per thread (local memory)
-constexpr int kKeepActive = 20;  // default: leave the traversal loop when fewer lanes than this are busy
-constexpr uint32_t kIdle = 0xFFFFFFFFu;
+constexpr int kKeepActive = 20;  // SCHED_WHILE: leave the traversal loop when fewer lanes are busy
+constexpr int kAdvanceAt = 8;    // SCHED_VOTE: run the advance step once this many lanes want it
+constexpr int kTriAt = 8;        // SCHED_VOTE: run the triangle step once this many lanes want it
+constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr uint32_t kChunk = 32;  // jobs per atomic fetch
+
+enum { SCHED_VOTE = 0, SCHED_WHILE = 1 };
 
 struct WideScene {
   const float4* nodes;  // Node4 array, 8 float4 each
   const float4* tris;   // srt_tri_rec_t array, 3 float4 each
-  int keep_active;      // refill threshold (VX_DCR_RT_KEEP_ACTIVE, default kKeepActive)
+  int tune;             // SCHED_VOTE: advance threshold | triangle threshold << 8; SCHED_WHILE: keep-active
 };
 
 enum { ST_PRIMARY = 0, ST_SHADOW1 = 1, ST_BOUNCE = 2, ST_SHADOW2 = 3 };
@@ -59,12 +71,23 @@ __device__ __forceinline__ void ray_setup(RayState& r, V3 o, V3 d, float tmin, b
   r.found = false;
 }
 
+// What a lane is doing inside the scene: a child ref as stored in Node4 -- an inner node index
+// (bit 31 clear), one triangle (bit 31 set) -- or kNone when its ray has ended.
+struct Cursor {
+  uint32_t ref;
+  __device__ __forceinline__ bool wants_node() const { return (int32_t)ref >= 0; }
+  __device__ __forceinline__ bool wants_tri() const { return (int32_t)ref < 0 && ref != kNone; }
+  __device__ __forceinline__ bool busy() const { return ref != kNone; }
+  __device__ __forceinline__ void clear() { ref = kNone; }
+  __device__ __forceinline__ void go(uint32_t r) { ref = r; }
+};
+
 // One traversal stack per thread: shared entries first, local spill above.
 struct Stack {
   uint2* sm;  // &s_stack[threadIdx.x]; entry i at sm[i * kWideThreads]
   uint2 spill[kLocalStack];
   int sp;
-  __device__ __forceinline__ void push(uint32_t ref, float tn) {
+  __device__ __forceinline__ void push_slow(uint32_t ref, float tn) {
     const uint2 e = make_uint2(ref, __float_as_uint(tn));
     if (sp < kSmStack) sm[sp * kWideThreads] = e;
     else if (sp < kSmStack + kLocalStack) spill[sp - kSmStack] = e;
@@ -77,92 +100,87 @@ struct Stack {
   }
 };
 
-// Pop until an entry survives the current closest distance; kIdle when the stack is empty.
-__device__ __forceinline__ uint32_t pop_next(Stack& st, const RayState& r, float best_t) {
+// Pop until an entry survives the current closest distance; kNone when the stack is empty.
+__device__ __forceinline__ uint32_t pop_next(Stack& st, float best_t) {
   while (st.sp > 0) {
     const uint2 e = st.pop();
     if (__uint_as_float(e.y) <= best_t * kPad) return e.x;
   }
-  return kIdle;
+  return kNone;
 }
 
-// ---- one inner node: test the four children, continue with the nearest, push the others --------
+// ---- NODE step: test the four children, continue with the nearest, push the others ---------------
 // Box test per child: entry = max(near planes, tmin), exit = min(far planes, best_t); the child
 // is visited when entry <= exit * kPad.  Boxes were inflated by the scene delta at repack time.
 template <bool STATS>
-__device__ __forceinline__ uint32_t inner_step(const WideScene& sc, uint32_t cur, const RayState& r, float best_t,
-                                               Stack& st, Stats& stats) {
-  const float4* np = sc.nodes + (size_t)cur * 8;
+__device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const RayState& r, float best_t, Stack& st,
+                                          Stats& stats) {
+  const float4* np = sc.nodes + (size_t)cu.ref * 8;
   const float4 nx = __ldg(np + r.ox), fx = __ldg(np + (r.ox ^ 1u));
   const float4 ny = __ldg(np + r.oy), fy = __ldg(np + (r.oy ^ 1u));
   const float4 nz = __ldg(np + r.oz), fz = __ldg(np + (r.oz ^ 1u));
   const float4 rf = __ldg(np + 6);
   if (STATS) stats.nodes += 1;
-  const float lim = best_t;
 #define SRT_CHILD(c, tn, hit)                                                                              \
   const float tn = fmaxf(fmaxf(__fmaf_rn(nx.c, r.idir.x, -r.ood.x), __fmaf_rn(ny.c, r.idir.y, -r.ood.y)), \
                          fmaxf(__fmaf_rn(nz.c, r.idir.z, -r.ood.z), r.tmin));                             \
   const bool hit = tn <= fminf(fminf(__fmaf_rn(fx.c, r.idir.x, -r.ood.x), __fmaf_rn(fy.c, r.idir.y, -r.ood.y)), \
-                               fminf(__fmaf_rn(fz.c, r.idir.z, -r.ood.z), lim)) * kPad;
+                               fminf(__fmaf_rn(fz.c, r.idir.z, -r.ood.z), best_t)) * kPad;
   SRT_CHILD(x, t0, h0)
   SRT_CHILD(y, t1, h1)
   SRT_CHILD(z, t2, h2)
   SRT_CHILD(w, t3, h3)
 #undef SRT_CHILD
-  // nearest hit child becomes the next node; the other hit children are pushed with their entry
-  // distance (checked again against the then-current closest distance when popped)
+  if (!(h0 | h1 | h2 | h3)) {
+    cu.go(pop_next(st, best_t));
+    return;
+  }
+  // nearest hit child becomes the next position; the other hit children are pushed with their
+  // entry distance (checked again against the then-current closest distance when popped)
   const float inf = __int_as_float(0x7f800000);
   const float k0 = h0 ? t0 : inf, k1 = h1 ? t1 : inf, k2 = h2 ? t2 : inf, k3 = h3 ? t3 : inf;
   const float kmin = fminf(fminf(k0, k1), fminf(k2, k3));
-  if (!(h0 | h1 | h2 | h3)) return pop_next(st, r, best_t);
-  uint32_t next;
-  int sel;
-  if (k0 == kmin) { sel = 0; next = __float_as_uint(rf.x); }
-  else if (k1 == kmin) { sel = 1; next = __float_as_uint(rf.y); }
-  else if (k2 == kmin) { sel = 2; next = __float_as_uint(rf.z); }
-  else { sel = 3; next = __float_as_uint(rf.w); }
-  if (h3 && sel != 3) st.push(__float_as_uint(rf.w), t3);
-  if (h2 && sel != 2) st.push(__float_as_uint(rf.z), t2);
-  if (h1 && sel != 1) st.push(__float_as_uint(rf.y), t1);
-  if (h0 && sel != 0) st.push(__float_as_uint(rf.x), t0);
-  return next;
+  const int sel = k0 == kmin ? 0 : (k1 == kmin ? 1 : (k2 == kmin ? 2 : 3));
+  const uint32_t c0 = __float_as_uint(rf.x), c1 = __float_as_uint(rf.y), c2 = __float_as_uint(rf.z),
+                 c3 = __float_as_uint(rf.w);
+  const uint32_t next = sel == 0 ? c0 : (sel == 1 ? c1 : (sel == 2 ? c2 : c3));
+  const bool p0 = h0 && sel != 0, p1 = h1 && sel != 1, p2 = h2 && sel != 2, p3 = h3 && sel != 3;
+  if (st.sp + 3 <= kSmStack) {  // common case: predicated stores, no branches
+    uint2* top = st.sm + st.sp * kWideThreads;
+    if (p3) { *top = make_uint2(c3, __float_as_uint(t3)); top += kWideThreads; }
+    if (p2) { *top = make_uint2(c2, __float_as_uint(t2)); top += kWideThreads; }
+    if (p1) { *top = make_uint2(c1, __float_as_uint(t1)); top += kWideThreads; }
+    if (p0) { *top = make_uint2(c0, __float_as_uint(t0)); }
+    st.sp += (int)p0 + (int)p1 + (int)p2 + (int)p3;
+  } else {
+    if (p3) st.push_slow(c3, t3);
+    if (p2) st.push_slow(c2, t2);
+    if (p1) st.push_slow(c1, t1);
+    if (p0) st.push_slow(c0, t0);
+  }
+  cu.go(next);
 }
 
-// ---- one leaf: up to eight triangles --------------------------------------------------------------
+// ---- TRIANGLE step: the ray/triangle test of the triangle the lane is at ----------------------------
 template <bool STATS>
-__device__ __forceinline__ void leaf_step(const WideScene& sc, uint32_t ref, RayState& r, Hit& best, Stats& stats) {
-  const uint32_t first = ref & 0x0FFFFFFFu, count = ((ref >> 28) & 7u) + 1u;
-  if (STATS) stats.tris += count;
+__device__ __forceinline__ void tri_step(const WideScene& sc, Cursor& cu, RayState& r, Hit& best, Stack& st,
+                                         Stats& stats) {
+  const uint32_t rec = cu.ref & 0x7FFFFFFFu;
+  if (STATS) stats.tris += 1;
   if (r.any) {
-    for (uint32_t i = 0; i < count; ++i) {
-      const float4* tp = sc.tris + 3 * (size_t)(first + i);
-      const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
-      float t, u, v;
-      if (intersect_tri(r0, r1, r2, r.o, r.d, t, u, v) && t > r.tmin && t < best.t) {
-        r.found = true;
-        return;
-      }
+    const float4* tp = sc.tris + 3 * (size_t)rec;
+    const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
+    float t, u, v;
+    if (intersect_tri(r0, r1, r2, r.o, r.d, t, u, v) && t > r.tmin && t < best.t) {
+      r.found = true;
+      st.sp = 0;
+      cu.clear();
+      return;
     }
   } else {
-    for (uint32_t i = 0; i < count; ++i) consider(sc.tris, first + i, r.o, r.d, r.tmin, best);
+    consider(sc.tris, rec, r.o, r.d, r.tmin, best);
   }
-}
-
-// ---- the generic traversal loop -------------------------------------------------------------------
-// cur: node/leaf ref the lane is at, kIdle when the lane has no ray in flight.  Returns when fewer
-// than kKeepActive lanes of the warp are still traversing (all 32 lanes must call this together).
-template <bool STATS>
-__device__ __forceinline__ void traverse(const WideScene& sc, uint32_t& cur, RayState& r, Hit& best, Stack& st,
-                                         Stats& stats) {
-  for (;;) {
-    while ((int32_t)cur >= 0) cur = inner_step<STATS>(sc, cur, r, best.t, st, stats);
-    if (cur != kIdle) {
-      leaf_step<STATS>(sc, cur, r, best, stats);
-      if (r.any && r.found) { st.sp = 0; cur = kIdle; }
-      else cur = pop_next(st, r, best.t);
-    }
-    if (__popc(__ballot_sync(0xffffffffu, cur != kIdle)) < sc.keep_active) return;
-  }
+  cu.go(pop_next(st, best.t));
 }
 
 // ---- job pool: a warp-uniform window [next, end) of job ids, refilled kChunk at a time ------------
@@ -171,7 +189,7 @@ struct Pool {
   bool dry;            // the global cursor ran past the last job
 };
 
-// Hands one job id to every lane with want == true (kIdle-style ~0u when none is left).
+// Hands one job id to every lane with want == true (~0u when none is left).  Warp-convergent.
 __device__ __forceinline__ uint32_t take_jobs(Pool& p, bool want, unsigned long long* cursor, uint32_t total_jobs) {
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t mask = __ballot_sync(0xffffffffu, want);
@@ -179,7 +197,7 @@ __device__ __forceinline__ uint32_t take_jobs(Pool& p, bool want, unsigned long 
   if (mask == 0u) return job;
   const uint32_t rank = __popc(mask & ((1u << lane) - 1u));
   uint32_t n = __popc(mask);
-  uint32_t have = p.end - p.next;
+  const uint32_t have = p.end - p.next;
   if (want && rank < have) job = p.next + rank;
   if (n <= have) {
     p.next += n;
@@ -207,6 +225,41 @@ __device__ __forceinline__ uint32_t take_jobs(Pool& p, bool want, unsigned long 
   return job;
 }
 
+// ---- the warp scheduler ----------------------------------------------------------------------------
+// advance(): warp-convergent; for every lane whose ray has ended it finishes / continues the lane's
+// job, then hands new jobs to lanes without one (sets have_job, cu, r, best).
+template <int SCHED, bool STATS, class Advance>
+__device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RayState& r, Hit& best, Stack& st,
+                                         Stats& stats, const Pool& pool, const bool& have_job, Advance advance) {
+  if (SCHED == SCHED_WHILE) {
+    for (;;) {
+      advance();
+      if (pool.dry && !__any_sync(0xffffffffu, have_job)) return;
+      for (;;) {
+        while (cu.wants_node()) node_step<STATS>(sc, cu, r, best.t, st, stats);
+        while (cu.wants_tri()) tri_step<STATS>(sc, cu, r, best, st, stats);
+        if (__popc(__ballot_sync(0xffffffffu, cu.busy())) < sc.tune) break;
+      }
+    }
+  } else {
+    for (;;) {
+      const bool wn = cu.wants_node(), wt = cu.wants_tri();
+      const bool wa = !wn && !wt && (have_job || !pool.dry);
+      const uint32_t mn = __ballot_sync(0xffffffffu, wn), mt = __ballot_sync(0xffffffffu, wt);
+      const uint32_t ma = __ballot_sync(0xffffffffu, wa);
+      if ((mn | mt | ma) == 0u) return;
+      // minority work (triangle tests, path advance) is batched until enough lanes want it
+      if (__popc(ma) >= (sc.tune & 0xff) || (mn | mt) == 0u) {
+        advance();
+      } else if (__popc(mt) >= ((sc.tune >> 8) & 0xff) || mn == 0u) {
+        if (wt) tri_step<STATS>(sc, cu, r, best, st, stats);
+      } else {
+        if (wn) node_step<STATS>(sc, cu, r, best.t, st, stats);
+      }
+    }
+  }
+}
+
 // ---- render kernel: every lane carries one pixel through all samples and path stages --------------
 struct PathState {
   uint32_t x, ly, pix;  // pixel, local (strip) row, frame pixel index (RNG key)
@@ -218,8 +271,8 @@ struct PathState {
   uint32_t alb1, alb2;  // packed albedo at the primary / bounce hit
 };
 
-template <bool STATS>
-__global__ void __launch_bounds__(kWideThreads, 3)
+template <int SCHED, bool STATS>
+__global__ void __launch_bounds__(kWideThreads, SRT_MIN_BLOCKS)
 rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc, uint32_t local_rows,
                       uint32_t total_jobs, unsigned long long* counters) {
   extern __shared__ uint2 s_stack[];
@@ -234,8 +287,10 @@ rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc
   RayState r;
   Hit best;
   Stats stats = {0u, 0u};
-  uint32_t cur = kIdle, n_shadow = 0u, n_bounce = 0u;
+  Cursor cu;
+  uint32_t n_shadow = 0u, n_bounce = 0u;
   bool have_job = false;
+  cu.clear();
   best.t = 0.0f; best.u = 0.0f; best.v = 0.0f; best.prim = SRT_MISS; best.rec = 0u;
   ray_setup(r, cam.eye, cam.fwd, 0.0f, false);
 
@@ -243,7 +298,7 @@ rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc
     ray_setup(r, o, d, 0.0f, any);
     best.t = tmax; best.prim = SRT_MISS; best.rec = 0u;
     st.sp = 0;
-    cur = 0u;  // root
+    cu.go(0u);  // root
   };
   auto start_primary = [&]() {
     float jx = 0.5f, jy = 0.5f;
@@ -252,9 +307,9 @@ rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc
     start_ray(cam.eye, camera_dir(cam, ps.x, global_row(a, ps.ly), jx, jy), kTMax, false);
   };
 
-  for (;;) {
+  auto advance = [&]() {
     // ---- lanes whose ray has ended advance their path ----------------------------------------
-    if (have_job && cur == kIdle) {
+    if (have_job && !cu.busy()) {
       V3 rad = ld3(a.sky);
       bool sample_done = false;
       if (ps.stage == ST_PRIMARY || ps.stage == ST_BOUNCE) {
@@ -274,21 +329,20 @@ rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc
           if (bounce) ps.alb2 = __float_as_uint(r1.w);
           else { ps.alb1 = __float_as_uint(r1.w); ps.n = sf.n; }
           ps.ndl = sf.ndl;
+          ps.stage = bounce ? ST_SHADOW2 : ST_SHADOW1;
           if (sf.ndl > 0.0f && a.mode >= SRT_MODE_SHADOW) {
             ++n_shadow;
-            ps.stage = bounce ? ST_SHADOW2 : ST_SHADOW1;
             start_ray(sf.po, sf.ld, sf.dist, true);
           } else {
-            // no shadow ray: fall through to the "shadow finished, visible" transition below
+            // no shadow ray: continue below as "shadow ray ended, light visible"
             r.o = sf.po;
             r.found = false;
-            if (!(sf.ndl > 0.0f)) ps.ndl = 0.0f;  // k = ambient exactly (ambient + 0*1)
-            ps.stage = bounce ? ST_SHADOW2 : ST_SHADOW1;
+            if (!(sf.ndl > 0.0f)) ps.ndl = 0.0f;  // direct term = ambient exactly
           }
         }
       }
-      if (!sample_done && cur == kIdle && (ps.stage == ST_SHADOW1 || ps.stage == ST_SHADOW2)) {
-        // direct term: ambient + n.l * visibility
+      if (!sample_done && !cu.busy() && (ps.stage == ST_SHADOW1 || ps.stage == ST_SHADOW2)) {
+        // direct term: ambient + n.l * visibility (visibility is 0 or 1, so the product is exact)
         const float k = (ps.ndl > 0.0f) ? (r.found ? a.ambient : a.ambient + ps.ndl) : a.ambient;
         if (ps.stage == ST_SHADOW1) {
           ps.k1 = k;
@@ -322,24 +376,23 @@ rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc
       }
     }
     // ---- lanes without a pixel take one from the warp's window (ballot + prefix popc) ---------
-    {
-      const uint32_t job = take_jobs(pool, !have_job, counters + CTR_CURSOR, total_jobs);
-      if (job != ~0u) {
-        const uint32_t tile = job >> 5, l = job & 31u;
-        ps.x = (tile % tiles_x) * 8u + (l & 7u);
-        ps.ly = (tile / tiles_x) * 4u + (l >> 3);
-        if (ps.x < W && ps.ly < local_rows) {
-          ps.pix = global_row(a, ps.ly) * W + ps.x;
-          ps.s = 0u;
-          ps.sum = mk(0.0f, 0.0f, 0.0f);
-          have_job = true;
-          start_primary();
-        }
+    const uint32_t job = take_jobs(pool, !have_job, counters + CTR_CURSOR, total_jobs);
+    if (job != ~0u) {
+      const uint32_t tile = job >> 5, l = job & 31u;
+      ps.x = (tile % tiles_x) * 8u + (l & 7u);
+      ps.ly = (tile / tiles_x) * 4u + (l >> 3);
+      if (ps.x < W && ps.ly < local_rows) {
+        ps.pix = global_row(a, ps.ly) * W + ps.x;
+        ps.s = 0u;
+        ps.sum = mk(0.0f, 0.0f, 0.0f);
+        have_job = true;
+        start_primary();
       }
     }
-    if (pool.dry && !__any_sync(0xffffffffu, have_job)) break;
-    traverse<STATS>(sc, cur, r, best, st, stats);
-  }
+  };
+
+  run_warp<SCHED, STATS>(sc, cu, r, best, st, stats, pool, have_job, advance);
+
   n_shadow = __reduce_add_sync(0xffffffffu, n_shadow);
   n_bounce = __reduce_add_sync(0xffffffffu, n_bounce);
   if ((threadIdx.x & 31u) == 0u) {
@@ -350,8 +403,8 @@ rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc
 }
 
 // ---- explicit ray list (mode 3): job = ray index, closest hit, 16-byte hit record out -------------
-template <bool STATS>
-__global__ void __launch_bounds__(kWideThreads, 3)
+template <int SCHED, bool STATS>
+__global__ void __launch_bounds__(kWideThreads, SRT_MIN_BLOCKS)
 rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, const WideScene sc,
                     uint32_t total_jobs, unsigned long long* counters) {
   extern __shared__ uint2 s_stack[];
@@ -362,12 +415,15 @@ rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
   RayState r;
   Hit best;
   Stats stats = {0u, 0u};
-  uint32_t cur = kIdle, my_ray = 0u;
+  Cursor cu;
+  uint32_t my_ray = 0u;
   bool have_job = false;
+  cu.clear();
   best.t = 0.0f; best.u = 0.0f; best.v = 0.0f; best.prim = SRT_MISS; best.rec = 0u;
   ray_setup(r, mk(0.0f, 0.0f, 0.0f), mk(0.0f, 0.0f, 1.0f), 0.0f, false);
-  for (;;) {
-    if (have_job && cur == kIdle) {
+
+  auto advance = [&]() {
+    if (have_job && !cu.busy()) {
       hits[my_ray] = make_float4(best.t, best.u, best.v, __uint_as_float(best.prim));
       have_job = false;
     }
@@ -379,11 +435,11 @@ rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
       ray_setup(r, mk(r0.x, r0.y, r0.z), mk(r1.x, r1.y, r1.z), r0.w, false);
       best.t = r1.w; best.u = 0.0f; best.v = 0.0f; best.prim = SRT_MISS; best.rec = 0u;
       st.sp = 0;
-      cur = 0u;
+      cu.go(0u);
     }
-    if (pool.dry && !__any_sync(0xffffffffu, have_job)) break;
-    traverse<STATS>(sc, cur, r, best, st, stats);
-  }
+  };
+
+  run_warp<SCHED, STATS>(sc, cu, r, best, st, stats, pool, have_job, advance);
   if (STATS) flush_stats(stats, counters);
 }
 

@@ -66,7 +66,8 @@ struct vx_device {
 // DCRs owned by this back-end (outside every range the reference decodes,
 // hw/rtl/VX_types.vh:23-29, :332-339, :353-359, :439-458).
 #define VX_DCR_RT_BASE    0x800
-#define VX_DCR_RT_VARIANT 0x800 /* 0 = default (wide BVH, wavefront), 1 = baseline BVH2 megakernel */
+#define VX_DCR_RT_VARIANT 0x800 /* 0 = default (Node4, persistent, vote scheduler), 1 = baseline BVH2 megakernel,
+                                   2 = Node4 persistent while-while (A/B)                                    */
 #define VX_DCR_RT_STATS   0x801 /* 1 = count node fetches / triangle tests (slower)               */
 #define VX_DCR_RT_KEEP_ACTIVE 0x802 /* tuning: refill threshold of the persistent kernels (1..32), 0 = default */
 #define VX_DCR_RT_END     0x810

@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "lib", "libvortex.so")
+LIB_PATH = os.environ.get("SKYBOX_RT_LIB") or os.path.join(PKG, "lib", "libvortex.so")  # env: A/B builds only
 
 # caps ids / flags (include/vortex.h)
 VX_CAPS_VERSION, VX_CAPS_NUM_THREADS, VX_CAPS_NUM_WARPS, VX_CAPS_NUM_CORES = 0, 1, 2, 3
@@ -30,7 +30,7 @@ VX_CSR_RT_NODE_BYTES, VX_CSR_RT_LAUNCHES = 0x7C6, 0x7C7
 
 # back-end DCRs (csrc/vx_internal.h)
 VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE = 0x800, 0x801, 0x802
-RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE = 0, 1
+RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE = 0, 1, 2
 
 EXPORTS = [
     "vx_dev_open", "vx_dev_close", "vx_dev_caps", "vx_mem_alloc", "vx_mem_reserve", "vx_mem_free",
