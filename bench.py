@@ -54,6 +54,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
     ap.add_argument("--keep-active", type=int, default=0, help="diagnostic: refill threshold DCR (0 = default)")
+    ap.add_argument("--prefetch", type=int, default=0, help="diagnostic: VX_DCR_RT_PREFETCH (2 = no L2 warm-up)")
     ap.add_argument("--mode", type=int, default=None, help="diagnostic: override the workload's shading mode (0/1/2)")
     ap.add_argument("--spp", type=int, default=None, help="diagnostic: override the workload's samples per pixel")
     return ap.parse_args()
@@ -214,6 +215,7 @@ def native_arm(args, wl):
     dev = tracer.dev
     dev.dcr_write(vx.VX_DCR_RT_VARIANT, args.variant)
     dev.dcr_write(vx.VX_DCR_RT_KEEP_ACTIVE, args.keep_active)
+    dev.dcr_write(vx.VX_DCR_RT_PREFETCH, args.prefetch)
     stream = torch.cuda.ExternalStream(dev.cuda_stream(), device=torch.device("cuda", local))
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.int32, device="cuda")
     launches = 0

@@ -14,6 +14,7 @@
 // clang-format off
 #include "rt_baseline.cuh"
 #include "rt_wide.cuh"
+#include "rt_pool.cuh"
 // clang-format on
 
 namespace srt {
@@ -35,6 +36,9 @@ struct RtState {
   unsigned long long* d_counters;  // CTR_COUNT u64, zeroed at every launch
   WideCache wide;
   int wide_blocks_per_sm[8];       // occupancy of the persistent kernels, queried once
+  int pool_blocks_per_sm[4];
+  uint2* d_spill;                  // stack spill area of the pool kernels (rarely touched)
+  size_t spill_warps;
 };
 
 static int rt_state(vx_device* dev, RtState** out) {
@@ -118,10 +122,37 @@ static int persistent_grid(vx_device* dev, int* cached, K kernel, size_t smem, u
   return (int)(need < full ? need : full);
 }
 
+// grid of a pool kernel (kPoolThreads per CTA, one 64-ray pool per warp) + its spill area
+template <class K>
+static int pool_grid(vx_device* dev, RtState* st, int* cached, K kernel, size_t smem, uint64_t jobs, int cap) {
+  if (*cached == 0) {
+    int n = 0;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kPoolThreads, smem) != cudaSuccess || n <= 0)
+      return -1;
+    *cached = n;
+  }
+  const int per_sm = cap > 0 && cap < *cached ? cap : *cached;
+  const uint64_t full = (uint64_t)dev->prop.multiProcessorCount * (uint64_t)per_sm;
+  const uint64_t need = (jobs + kPoolSlots * (kPoolThreads / 32) - 1) / (kPoolSlots * (kPoolThreads / 32));
+  const int grid = (int)(need < full ? need : full);
+  const size_t warps = (size_t)grid * (kPoolThreads / 32);
+  if (warps > st->spill_warps) {
+    if (st->d_spill) cudaFree(st->d_spill);
+    st->d_spill = nullptr;
+    st->spill_warps = 0;
+    const size_t w = (size_t)dev->prop.multiProcessorCount * (size_t)*cached * (kPoolThreads / 32);
+    if (cudaMalloc(&st->d_spill, w * kPoolSlots * kPoolSpill * sizeof(uint2)) != cudaSuccess) return -1;
+    st->spill_warps = w;
+  }
+  return grid;
+}
+
 void rt_destroy(vx_device* dev) {
   if (!dev->rt) return;
   cudaFree(dev->rt->d_counters);
   if (dev->rt->wide.d_nodes4) cudaFree(dev->rt->wide.d_nodes4);
+  if (dev->rt->d_spill) cudaFree(dev->rt->d_spill);
   delete dev->rt;
   dev->rt = nullptr;
 }
@@ -149,17 +180,24 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   cudaStream_t s = dev->stream;
   const bool stats = dev->dcrs.count(VX_DCR_RT_STATS) && dev->dcrs[VX_DCR_RT_STATS] != 0;
   const uint32_t variant = dev->dcrs.count(VX_DCR_RT_VARIANT) ? dev->dcrs[VX_DCR_RT_VARIANT] : 0u;
-  if (variant > 2u) {
+  if (variant > 3u) {
     fprintf(stderr, "[VXDRV] raytrace: unknown kernel variant %u\n", variant);
     return -1;
   }
   const bool wide = variant != 1u;
+  const bool pooled = variant == 3u;
   const int sched = variant == 2u ? SCHED_WHILE : SCHED_VOTE;
   dev->last_launches = 0;
   dev->last_node_bytes = wide ? (uint32_t)sizeof(Node4) : 32u;
   if (wide && wide_prepare(dev, st, a) != 0) return -1;
   uint32_t tune = dev->dcrs.count(VX_DCR_RT_KEEP_ACTIVE) ? dev->dcrs[VX_DCR_RT_KEEP_ACTIVE] : 0u;
-  if (sched == SCHED_WHILE) {
+  const int pool_cap = (int)((tune >> 16) & 0xffu);  // tuning: CTAs per SM of the pool kernels (0 = all that fit)
+  if (pooled) {
+    uint32_t tf = tune & 0xffu, tt = (tune >> 8) & 0xffu;
+    if (tf == 0u || tf > 64u) tf = kPoolFetchAt;
+    if (tt == 0u || tt > 64u) tt = kPoolTriAt;
+    tune = tf | (tt << 8);
+  } else if (sched == SCHED_WHILE) {
     if (tune == 0u || tune > 32u) tune = kKeepActive;
   } else {
     uint32_t ta = tune & 0xffu, tt = (tune >> 8) & 0xffu;
@@ -171,6 +209,18 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   const size_t smem = sizeof(uint2) * kSmStack * kWideThreads;
   int* occ = st->wide_blocks_per_sm + (sched * 4 + (stats ? 2 : 0));
   VX_CUDA_OK(cudaMemsetAsync(st->d_counters, 0, sizeof(unsigned long long) * CTR_COUNT, s));
+
+  uint32_t extra_launches = 0;
+  {
+    const uint32_t pf = dev->dcrs.count(VX_DCR_RT_PREFETCH) ? dev->dcrs[VX_DCR_RT_PREFETCH] : 0u;
+    const size_t nb = (size_t)st->wide.num_nodes4 * sizeof(Node4), tbytes = (size_t)a.num_tris * sizeof(srt_tri_rec_t);
+    if (wide && pf == 1u && nb + tbytes <= (size_t)dev->prop.l2CacheSize * 3 / 4) {
+      rt_prefetch_l2_kernel<<<dev->prop.multiProcessorCount * 4, 256, 0, s>>>(
+          reinterpret_cast<const char*>(st->wide.d_nodes4), nb / 128, reinterpret_cast<const char*>(a.tri_addr),
+          (tbytes + 127) / 128);
+      extra_launches = 1;
+    }
+  }
 
 // launch one of the four instantiations of a persistent kernel
 #define SRT_LAUNCH_WIDE(KERNEL, OCC, JOBS, ...)                                                    \
@@ -197,7 +247,20 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
     const uint64_t slice = 1ull << 30;
     for (uint64_t first = 0; first < a.num_rays; first += slice) {
       const uint64_t n = a.num_rays - first < slice ? a.num_rays - first : slice;
-      if (wide) {
+      if (pooled) {
+        const float4* rays = reinterpret_cast<const float4*>(a.ray_addr) + 2 * first;
+        float4* hits = reinterpret_cast<float4*>(a.hit_addr) + first;
+        if (first) VX_CUDA_OK(cudaMemsetAsync(st->d_counters + CTR_CURSOR, 0, sizeof(unsigned long long), s));
+        const size_t psmem = sizeof(WarpPool) * (kPoolThreads / 32);
+        int g;
+        if (stats) {
+          if ((g = pool_grid(dev, st, &st->pool_blocks_per_sm[0], rt_pool_rays_kernel<true>, psmem, n, pool_cap)) <= 0) return -1;
+          rt_pool_rays_kernel<true><<<g, kPoolThreads, psmem, s>>>(rays, hits, sc, st->d_spill, (uint32_t)n, st->d_counters);
+        } else {
+          if ((g = pool_grid(dev, st, &st->pool_blocks_per_sm[1], rt_pool_rays_kernel<false>, psmem, n, pool_cap)) <= 0) return -1;
+          rt_pool_rays_kernel<false><<<g, kPoolThreads, psmem, s>>>(rays, hits, sc, st->d_spill, (uint32_t)n, st->d_counters);
+        }
+      } else if (wide) {
         const float4* rays = reinterpret_cast<const float4*>(a.ray_addr) + 2 * first;
         float4* hits = reinterpret_cast<float4*>(a.hit_addr) + first;
         if (first) VX_CUDA_OK(cudaMemsetAsync(st->d_counters + CTR_CURSOR, 0, sizeof(unsigned long long), s));
@@ -214,6 +277,7 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
       VX_CUDA_OK(cudaGetLastError());
       dev->last_launches += 1;
     }
+    dev->last_launches += extra_launches;
     return 0;
   }
 
@@ -232,7 +296,7 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   }
 #undef SRT_LAUNCH_WIDE
   VX_CUDA_OK(cudaGetLastError());
-  dev->last_launches = 1;
+  dev->last_launches = 1 + extra_launches;
   return 0;
 }
 

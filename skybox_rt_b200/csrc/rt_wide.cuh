@@ -260,6 +260,16 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
   }
 }
 
+// ---- L2 warm-up: one prefetch per 128-byte line of the scene (used when the scene fits in L2, so
+// that first touches inside the traversal kernels cost an L2 hit instead of an HBM round trip) ----
+__global__ void __launch_bounds__(256) rt_prefetch_l2_kernel(const char* a, size_t lines_a, const char* b, size_t lines_b) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < lines_a + lines_b; i += stride) {
+    const char* p = i < lines_a ? a + i * 128 : b + (i - lines_a) * 128;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  }
+}
+
 // ---- render kernel: every lane carries one pixel through all samples and path stages --------------
 struct PathState {
   uint32_t x, ly, pix;  // pixel, local (strip) row, frame pixel index (RNG key)

@@ -70,6 +70,7 @@ struct vx_device {
                                    2 = Node4 persistent while-while (A/B)                                    */
 #define VX_DCR_RT_STATS   0x801 /* 1 = count node fetches / triangle tests (slower)               */
 #define VX_DCR_RT_KEEP_ACTIVE 0x802 /* tuning: refill threshold of the persistent kernels (1..32), 0 = default */
+#define VX_DCR_RT_PREFETCH 0x803 /* 1 = warm L2 with the scene before tracing when it fits (measured: no gain, off by default) */
 #define VX_DCR_RT_END     0x810
 
 namespace srt {

@@ -29,8 +29,8 @@ VX_CSR_RT_NODES, VX_CSR_RT_TRIS, VX_CSR_RT_ELAPSED_NS = 0x7C3, 0x7C4, 0x7C5
 VX_CSR_RT_NODE_BYTES, VX_CSR_RT_LAUNCHES = 0x7C6, 0x7C7
 
 # back-end DCRs (csrc/vx_internal.h)
-VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE = 0x800, 0x801, 0x802
-RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE = 0, 1, 2
+VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE, VX_DCR_RT_PREFETCH = 0x800, 0x801, 0x802, 0x803
+RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL = 0, 1, 2, 3
 
 EXPORTS = [
     "vx_dev_open", "vx_dev_close", "vx_dev_caps", "vx_mem_alloc", "vx_mem_reserve", "vx_mem_free",
