@@ -1,0 +1,46 @@
+"""world_size-2 (and 3) CPU test of the N>1 path's host logic over gloo: each rank renders ITS rows of the
+frame (with the CPU oracle standing in for the GPU kernel -- test infrastructure), the product's
+FrameGather assembles them on rank 0, and the result must equal the single-rank frame bit for bit."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, w, h, rpb, out_path):
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import _oracle as o
+    from skybox_rt_b200.multi import FrameGather
+    nodes, tris = o.bvh2_build(o.scene_cornell())
+    a = o.make_arg(w, h, 2, spp=2, seed=77)
+    a.num_ranks, a.rank_id, a.rows_per_block = world, rank, rpb
+    strip, _ = o.render(a, nodes, tris, threads=1)
+    g = FrameGather(w, h, rpb, torch.device("cpu"))
+    assert g.rows == strip.shape[0]
+    frame = g.gather(torch.from_numpy(strip.view(np.int32)))
+    if rank == 0:
+        np.save(out_path, frame.numpy().view(np.uint32))
+    else:
+        assert frame is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,w,h,rpb,port", [(2, 40, 30, 4, 29531), (3, 33, 17, 8, 29532), (2, 16, 3, 8, 29533)])
+def test_strips_gathered_over_gloo_equal_single_rank_frame(tmp_path, world, w, h, rpb, port):
+    import _oracle as o
+    out = str(tmp_path / "frame.npy")
+    mp.spawn(_worker, args=(world, port, w, h, rpb, out), nprocs=world, join=True)
+    nodes, tris = o.bvh2_build(o.scene_cornell())
+    full, _ = o.render(o.make_arg(w, h, 2, spp=2, seed=77), nodes, tris, threads=1)
+    assert np.array_equal(np.load(out), full)
