@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel, 2 wide while-while")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N>1: weak = samples per pixel x N (per-GPU work fixed), strong = the same frame split N ways")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
     ap.add_argument("--keep-active", type=int, default=0, help="diagnostic: refill threshold DCR (0 = default)")
@@ -174,7 +176,7 @@ def reference_arm(args, wl):
     print(json.dumps({
         "impl": "reference", "metric": "Mrays/s (primary+shadow+bounce rays traced)", "value": v, "unit": "Mrays/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["name"]},
         "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -264,17 +266,11 @@ def native_arm(args, wl):
         h2d, d2h = 192, (H * W * 4 if rank == 0 else 0)
         if world > 1:
             # one NCCL gather of the strips per frame, on the render stream
-            send = torch.zeros(max_rows * W, dtype=torch.int32, device="cuda")
-            recv = [torch.empty(max_rows * W, dtype=torch.int32, device="cuda") for _ in range(world)] \
-                if rank == 0 else None
-            from skybox_rt_b200.formats import rank_row_index
-            row_idx = [torch.as_tensor(rank_row_index(H, ROWS_PER_BLOCK, world, r), device="cuda")
-                       for r in range(world)] if rank == 0 else None
-            frame_dev = torch.empty((H, W), dtype=torch.int32, device="cuda") if rank == 0 else None
+            from skybox_rt_b200.multi import FrameGather
+            fg = FrameGather(W, H, ROWS_PER_BLOCK, torch.device("cuda", local))
 
             def gather():
-                send[:rows * W].copy_(strip.view(torch.int32), non_blocking=True)
-                dist.gather(send, recv, dst=0)
+                return fg.gather(strip.view(torch.int32))
         else:
             gather = None
 
@@ -287,11 +283,8 @@ def native_arm(args, wl):
             dev.start(tracer.kernel, tracer.args)
             if gather:
                 with torch.cuda.stream(stream):
-                    gather()
-                    if rank == 0:  # de-interleave the strips on the device, one D2H copy of the frame
-                        for r in range(world):
-                            n = len(row_idx[r])
-                            frame_dev.index_copy_(0, row_idx[r], recv[r][:n * W].view(n, W))
+                    frame_dev = gather()  # strips -> rank 0, de-interleaved on the device
+                    if rank == 0:         # one D2H copy of the assembled frame
                         host_frame.copy_(frame_dev.view(-1), non_blocking=True)
                 stream.synchronize()
             else:
@@ -379,6 +372,11 @@ def main():
     if args.spp is not None and wl["mode"] != 3:
         wl["spp"] = args.spp
         wl["name"] += f" [diagnostic: spp {args.spp}]"
+    if args.gpus > 1 and args.scaling == "weak" and wl["mode"] != 3:
+        # weak scaling: rows are split over the N ranks and every pixel takes N x the samples, so the
+        # rays per GPU stay those of the 1-GPU frame while the whole job grows N-fold
+        wl["spp"] = wl["spp"] * args.gpus
+        wl["name"] += f" [weak scaling: spp x {args.gpus} = {wl['spp']}]"
     if args.impl == "reference":
         reference_arm(args, wl)
         return
@@ -407,7 +405,7 @@ def main():
         out = {
             "metric": "Mrays/s (primary+shadow+bounce rays traced)", "value": value, "unit": "Mrays/s",
             "n_gpus": r["world"], "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": wl["name"], "triangles": r["n_tris"], "bvh2_nodes": r["n_nodes"],
                        "rays_per_step": int(r["rays_total"]), "kernel_variant": args.variant,
