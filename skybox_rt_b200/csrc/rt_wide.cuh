@@ -82,21 +82,33 @@ struct Cursor {
   __device__ __forceinline__ void go(uint32_t r) { ref = r; }
 };
 
-// One traversal stack per thread: shared entries first, local spill above.
+// Shared-memory accesses are written as PTX so that they stay `st.shared` / `ld.shared` with a 32-bit
+// address (as a struct member the pointer degraded to generic 64-bit ST.E / LD.E).
+__device__ __forceinline__ void sts64(uint32_t addr, uint32_t x, uint32_t y) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+  return v;
+}
+
+// One traversal stack per thread: shared entries first ([entry][thread]), local spill above.  The spill
+// array is a separate kernel-local array (passed by pointer) so that `sp` and `base` stay in registers.
+constexpr uint32_t kStackStride = kWideThreads * 8u;  // bytes between consecutive entries of one thread
 struct Stack {
-  uint2* sm;  // &s_stack[threadIdx.x]; entry i at sm[i * kWideThreads]
-  uint2 spill[kLocalStack];
+  uint32_t base;  // shared-space byte address of this thread's entry 0
+  uint2* spill;   // kLocalStack entries in local memory
   int sp;
   __device__ __forceinline__ void push_slow(uint32_t ref, float tn) {
-    const uint2 e = make_uint2(ref, __float_as_uint(tn));
-    if (sp < kSmStack) sm[sp * kWideThreads] = e;
-    else if (sp < kSmStack + kLocalStack) spill[sp - kSmStack] = e;
+    if (sp < kSmStack) sts64(base + (uint32_t)sp * kStackStride, ref, __float_as_uint(tn));
+    else if (sp < kSmStack + kLocalStack) spill[sp - kSmStack] = make_uint2(ref, __float_as_uint(tn));
     else __trap();  // the host checked 3 * depth <= capacity before launching
     ++sp;
   }
   __device__ __forceinline__ uint2 pop() {
     --sp;
-    return sp < kSmStack ? sm[sp * kWideThreads] : spill[sp - kSmStack];
+    return sp < kSmStack ? lds64(base + (uint32_t)sp * kStackStride) : spill[sp - kSmStack];
   }
 };
 
@@ -146,11 +158,11 @@ __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const
   const uint32_t next = sel == 0 ? c0 : (sel == 1 ? c1 : (sel == 2 ? c2 : c3));
   const bool p0 = h0 && sel != 0, p1 = h1 && sel != 1, p2 = h2 && sel != 2, p3 = h3 && sel != 3;
   if (st.sp + 3 <= kSmStack) {  // common case: predicated stores, no branches
-    uint2* top = st.sm + st.sp * kWideThreads;
-    if (p3) { *top = make_uint2(c3, __float_as_uint(t3)); top += kWideThreads; }
-    if (p2) { *top = make_uint2(c2, __float_as_uint(t2)); top += kWideThreads; }
-    if (p1) { *top = make_uint2(c1, __float_as_uint(t1)); top += kWideThreads; }
-    if (p0) { *top = make_uint2(c0, __float_as_uint(t0)); }
+    uint32_t top = st.base + (uint32_t)st.sp * kStackStride;
+    if (p3) { sts64(top, c3, __float_as_uint(t3)); top += kStackStride; }
+    if (p2) { sts64(top, c2, __float_as_uint(t2)); top += kStackStride; }
+    if (p1) { sts64(top, c1, __float_as_uint(t1)); top += kStackStride; }
+    if (p0) { sts64(top, c0, __float_as_uint(t0)); }
     st.sp += (int)p0 + (int)p1 + (int)p2 + (int)p3;
   } else {
     if (p3) st.push_slow(c3, t3);
@@ -286,8 +298,10 @@ __global__ void __launch_bounds__(kWideThreads, SRT_MIN_BLOCKS)
 rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc, uint32_t local_rows,
                       uint32_t total_jobs, unsigned long long* counters) {
   extern __shared__ uint2 s_stack[];
+  uint2 spill[kLocalStack];
   Stack st;
-  st.sm = s_stack + threadIdx.x;
+  st.base = (uint32_t)__cvta_generic_to_shared(s_stack + threadIdx.x);
+  st.spill = spill;
   st.sp = 0;
   const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
   const uint32_t seed_hash = mix32(a.seed);
@@ -418,8 +432,10 @@ __global__ void __launch_bounds__(kWideThreads, SRT_MIN_BLOCKS)
 rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, const WideScene sc,
                     uint32_t total_jobs, unsigned long long* counters) {
   extern __shared__ uint2 s_stack[];
+  uint2 spill[kLocalStack];
   Stack st;
-  st.sm = s_stack + threadIdx.x;
+  st.base = (uint32_t)__cvta_generic_to_shared(s_stack + threadIdx.x);
+  st.spill = spill;
   st.sp = 0;
   Pool pool = {0u, 0u, false};
   RayState r;
