@@ -35,7 +35,7 @@ constexpr int kWideThreads = 256;
 constexpr int kSmStack = SRT_SM_STACK;  // shared-memory stack entries per thread
 constexpr int kLocalStack = 80;  // spill entries per thread (local memory)
 constexpr int kKeepActive = 20;  // SCHED_WHILE: leave the traversal loop when fewer lanes are busy
-constexpr int kAdvanceAt = 8;    // SCHED_VOTE: run the advance step once this many lanes want it
+constexpr int kAdvanceAt = 16;   // SCHED_VOTE: run the advance step once this many lanes want it
 constexpr int kTriAt = 8;        // SCHED_VOTE: run the triangle step once this many lanes want it
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr uint32_t kChunk = 32;  // jobs per atomic fetch
