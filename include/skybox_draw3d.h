@@ -129,6 +129,11 @@ extern "C" {
 #define VX_DCR_OM_STATE_END (VX_DCR_OM_STATE_BEGIN + 18)
 #define VX_DCR_OM_STATE_COUNT 18
 
+/* Counters of the last draw, read with vx_mpm_query (free user-CSR numbers next to the RT ones). */
+#define VX_CSR_RASTER_FRAGMENTS 0x7C8  /* fragments shaded            (needs VX_DCR_RT_STATS = 1) */
+#define VX_CSR_RASTER_QUAD_TESTS 0x7C9 /* quad x primitive tests      (needs VX_DCR_RT_STATS = 1) */
+#define VX_CSR_RASTER_TILES 0x7CA      /* tiles (= CTAs) of the draw                                */
+
 /* ---- device-visible records: sim/common/graphics.h:38-71 ---------------------------------------- */
 typedef struct { int32_t x, y, z; } rast_vec3e_t;     /* fixed 16.16 (FloatE, graphics.h:26-31)        */
 typedef struct { int32_t x, y, z; } rast_attrib_t;    /* fixed 8.24  (FloatA): d(v0-v2), d(v1-v2), v2  */
@@ -219,14 +224,30 @@ const srt_texture_t* srt_trace_texture(const srt_trace_t* trace, uint32_t id);
 /* ---- host pre-pass: triangle setup + tile binning (role of graphics::Binning,
  * sim/common/gfxutil.cpp:103-276).  Same bytes as the reference for primbuf; tilebuf holds the same
  * tiles with the same pid lists in the same (tile_x, tile_y)-lexicographic order. ------------------ */
+/* The reference's tile header holds pids_offset and pids_count in 16 bits (graphics.h:66-71), which
+ * overflows once a draw bins more than ~64 K (tile, primitive) pairs -- any B200-sized frame.  The wide
+ * layout is this back-end's extension for those: selected per draw with VX_DCR_RASTER_EXT_TBUF_FORMAT. */
+#define SRT_TILEBUF_REFERENCE 0 /* rast_tile_header_t[num_tiles], then u32 pids                        */
+#define SRT_TILEBUF_WIDE 1      /* srt_tile_header_wide_t[num_tiles], then u32 pids                    */
+typedef struct {
+  uint16_t tile_x, tile_y;
+  uint32_t pids_count;
+  uint32_t pids_offset; /* in u32s, from the first pid after the last header */
+  uint32_t reserved;
+} srt_tile_header_wide_t; /* 16 B */
+#define VX_DCR_RASTER_EXT_TBUF_FORMAT 0x804 /* back-end DCR (outside the reference's ranges); 0 after open */
+
 typedef struct {
   uint8_t* tilebuf;   uint64_t tilebuf_size;
   uint8_t* primbuf;   uint64_t primbuf_size;
   uint32_t num_tiles; uint32_t num_prims;
   uint64_t num_tile_prims; /* sum of pids_count */
+  uint32_t format;         /* SRT_TILEBUF_* */
 } srt_binning_t;
+/* Returns 0; -1 on bad arguments / out of memory; -2 when `format` is SRT_TILEBUF_REFERENCE and a
+ * 16-bit field would overflow (the reference would truncate silently). */
 int srt_draw3d_binning(const srt_drawcall_t* draw, uint32_t width, uint32_t height, uint32_t tile_logsize,
-                       srt_binning_t* out);
+                       uint32_t format, srt_binning_t* out);
 void srt_binning_free(srt_binning_t* b);
 
 /* Texture upload image: level 0 followed by the box-filtered mip chain, and the per-level offsets the

@@ -76,7 +76,7 @@ def build(force=False, verbose=False):
     host_src = _glob(os.path.join(CSRC, "host"), (".c",))
     host_so = os.path.join(LIB, "libskybox_rt_host.so")
     if force or _stale(host_so, host_src + headers):
-        _run([CC] + HOST_CFLAGS + ["-shared", "-o", host_so] + host_src + ["-lm"], verbose)
+        _run([CC] + HOST_CFLAGS + ["-shared", "-o", host_so] + host_src + ["-lm", "-lz"], verbose)
 
     # 2. the CUDA back-end
     cu_src = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cpp"))]

@@ -96,6 +96,9 @@ int vx_dev_open(vx_device_h* hdevice) {
   dev->buffers = nullptr;
   dev->bytes_used = 0;
   dev->rt = nullptr;
+  dev->raster = nullptr;
+  dev->last_raster_tiles = 0;
+  dev->last_raster_fragments = dev->last_raster_tests = 0;
   dev->run_recorded = false;
   dev->last_rays_primary = 0;
   dev->last_counters_valid = false;
@@ -121,6 +124,7 @@ int vx_dev_close(vx_device_h hdevice) {
   cudaStreamSynchronize(dev->stream);
   if (env_int("VORTEX_PROFILING", 0) != 0) vx_dump_perf(hdevice, stdout);  // stub/vortex.cpp:99-104
   srt::rt_destroy(dev);
+  srt::raster_destroy(dev);
   while (dev->buffers) destroy_buffer(dev->buffers);  // apps leak their per-draw args buffers
   cudaEventDestroy(dev->ev_start);
   cudaEventDestroy(dev->ev_stop);
@@ -142,7 +146,7 @@ int vx_dev_caps(vx_device_h hdevice, uint32_t caps_id, uint64_t* value) {
     case VX_CAPS_LOCAL_MEM_SIZE: *value = (uint64_t)dev->prop.sharedMemPerMultiprocessor; break;
     case VX_CAPS_ISA_FLAGS:
       *value = VX_ISA_STD_A | VX_ISA_STD_F | VX_ISA_STD_D | VX_ISA_STD_I | VX_ISA_EXT_ICACHE | VX_ISA_EXT_DCACHE |
-               VX_ISA_EXT_L2CACHE | VX_ISA_EXT_LMEM | VX_ISA_EXT_RT;
+               VX_ISA_EXT_L2CACHE | VX_ISA_EXT_LMEM | VX_ISA_EXT_RT | VX_ISA_EXT_TEX | VX_ISA_EXT_RASTER | VX_ISA_EXT_OM;
       break;
     default:
       fprintf(stderr, "[VXDRV] invalid caps id: %u\n", caps_id);
@@ -259,6 +263,16 @@ int vx_start(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments) {
       rc = srt::rt_launch(dev, a);
       break;
     }
+    case SRT_PIPELINE_DRAW3D: {
+      draw3d_kernel_arg_t a;
+      if (!args->shadow || args->size < sizeof(a)) {
+        fprintf(stderr, "[VXDRV] vx_start: arguments buffer too small for the draw3d kernel_arg_t\n");
+        return -1;
+      }
+      memcpy(&a, args->shadow, sizeof(a));
+      rc = srt::raster_launch(dev, a);
+      break;
+    }
     default:
       fprintf(stderr, "[VXDRV] vx_start: unknown pipeline %u\n", img.pipeline);
       return -1;
@@ -323,6 +337,22 @@ int vx_mpm_query(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t*
   float ms = 0.0f;
   if (dev->run_recorded) VX_CUDA_OK(cudaEventElapsedTime(&ms, dev->ev_start, dev->ev_stop));
   if (!dev->last_counters_valid && dev->last_pipeline == SRT_PIPELINE_RAYTRACE) srt::rt_read_counters(dev);
+  if (dev->last_pipeline == SRT_PIPELINE_DRAW3D) {
+    if (!dev->last_counters_valid) {
+      srt::raster_read_counters(dev);
+      dev->last_counters_valid = true;
+    }
+    switch (addr) {
+      case VX_CSR_MCYCLE: *value = (uint64_t)((double)ms * 1e-3 * (double)dev->prop.clockRate * 1e3); return 0;
+      case VX_CSR_MINSTRET: *value = dev->last_raster_fragments; return 0;
+      case VX_CSR_RASTER_FRAGMENTS: *value = dev->last_raster_fragments; return 0;
+      case VX_CSR_RASTER_QUAD_TESTS: *value = dev->last_raster_tests; return 0;
+      case VX_CSR_RASTER_TILES: *value = dev->last_raster_tiles; return 0;
+      case VX_CSR_RT_ELAPSED_NS: *value = (uint64_t)((double)ms * 1e6); return 0;
+      case VX_CSR_RT_LAUNCHES: *value = dev->last_launches; return 0;
+      default: return -1;
+    }
+  }
   const uint64_t* c = dev->last_counters;
   switch (addr) {
     case VX_CSR_MCYCLE: *value = (uint64_t)((double)ms * 1e-3 * (double)dev->prop.clockRate * 1e3); break;

@@ -11,6 +11,7 @@
 #include <map>
 #include <mutex>
 
+#include "skybox_draw3d.h"
 #include "skybox_rt.h"
 #include "vortex.h"
 
@@ -41,7 +42,8 @@ enum {
 };
 
 namespace srt {
-struct RtState;  // rt_pipeline.cu
+struct RtState;      // rt_pipeline.cu
+struct RasterState;  // raster_pipeline.cu
 }
 
 struct vx_device {
@@ -61,6 +63,11 @@ struct vx_device {
   int last_pipeline;
   uint32_t last_launches;       // kernels enqueued by the last vx_start
   uint32_t last_node_bytes;     // bytes per node fetch of the kernel variant that ran
+  // raster pipeline (draw3d)
+  srt::RasterState* raster;
+  uint32_t last_raster_tiles;       // tiles (= CTAs) of the last draw
+  uint64_t last_raster_fragments;   // fragments shaded    (only when VX_DCR_RT_STATS is on)
+  uint64_t last_raster_tests;       // quad x primitive coverage tests (only when VX_DCR_RT_STATS is on)
 };
 
 // DCRs owned by this back-end (outside every range the reference decodes,
@@ -78,6 +85,10 @@ namespace srt {
 int rt_launch(vx_device* dev, const kernel_arg_t& arg);
 void rt_destroy(vx_device* dev);
 int rt_read_counters(vx_device* dev);
+// raster_pipeline.cu
+int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg);
+int raster_read_counters(vx_device* dev);
+void raster_destroy(vx_device* dev);
 }  // namespace srt
 
 #define VX_CUDA_OK(expr)                                                                          \
