@@ -220,6 +220,7 @@ int srt_trace_load(const char* path, srt_trace_t* out);
 int srt_trace_from_blob(const void* blob, uint64_t size, srt_trace_t* out);
 void srt_trace_free(srt_trace_t* trace);
 const srt_texture_t* srt_trace_texture(const srt_trace_t* trace, uint32_t id);
+const srt_drawcall_t* srt_drawcall_at(const srt_trace_t* trace, uint32_t index); /* NULL when out of range */
 
 /* ---- host pre-pass: triangle setup + tile binning (role of graphics::Binning,
  * sim/common/gfxutil.cpp:103-276).  Same bytes as the reference for primbuf; tilebuf holds the same
@@ -248,6 +249,9 @@ typedef struct {
  * 16-bit field would overflow (the reference would truncate silently). */
 int srt_draw3d_binning(const srt_drawcall_t* draw, uint32_t width, uint32_t height, uint32_t tile_logsize,
                        uint32_t format, srt_binning_t* out);
+/* Same, keeping only the tile rows of one rank: tile_y % num_ranks == rank (multi-GPU sharding). */
+int srt_draw3d_binning_rank(const srt_drawcall_t* draw, uint32_t width, uint32_t height, uint32_t tile_logsize,
+                            uint32_t format, uint32_t rank, uint32_t num_ranks, srt_binning_t* out);
 void srt_binning_free(srt_binning_t* b);
 
 /* Texture upload image: level 0 followed by the box-filtered mip chain, and the per-level offsets the

@@ -159,7 +159,17 @@ typedef struct { uint32_t key, pid; } o_pair_t; /* key = tile_x << 16 | tile_y :
 typedef struct {
   rast_prim_t* prims; uint32_t num_prims;
   uint8_t* tilebuf; uint64_t tilebuf_size; uint32_t num_tiles;
+  /* the same tiles without the 16-bit limits of rast_tile_header_t (pids_offset / pids_count wrap beyond
+   * 64 K entries, graphics.h:66-71): what the oracle's own kernel walks, so that it stays usable as a
+   * checker at frame sizes the reference's buffer format cannot describe */
+  uint32_t* tile_xy;    /* tile_x << 16 | tile_y, per tile */
+  uint32_t* tile_start; /* num_tiles + 1 offsets into pid_list */
+  uint32_t* pid_list;
 } o_bins_t;
+
+static void o_bins_free(o_bins_t* b) {
+  free(b->tilebuf); free(b->prims); free(b->tile_xy); free(b->tile_start); free(b->pid_list);
+}
 
 static void load_vertex(const o_draw_t* d, uint32_t i, v4* pos, float col[4], float uv[2]) {
   const uint8_t* p = d->verts + (uint64_t)i * 40;
@@ -270,6 +280,17 @@ static int o_binning(o_bins_t* out, const o_draw_t* d, uint32_t width, uint32_t 
       }
     }
     out->num_tiles = ntiles;
+    out->tile_xy = (uint32_t*)malloc((ntiles + 1) * sizeof(uint32_t));
+    out->tile_start = (uint32_t*)malloc((ntiles + 1) * sizeof(uint32_t));
+    out->pid_list = (uint32_t*)malloc((npairs ? npairs : 1) * sizeof(uint32_t));
+    {
+      uint32_t t = 0;
+      for (i = 0; i < npairs; ++i) {
+        if (i == 0 || src[i].key != src[i - 1].key) { out->tile_xy[t] = src[i].key; out->tile_start[t] = i; ++t; }
+        out->pid_list[i] = src[i].pid;
+      }
+      out->tile_start[t] = npairs;
+    }
     free(order);
     if (src == pairs) { free(sorted); } else { free(pairs); pairs = sorted; }
   }
@@ -285,6 +306,7 @@ static int o_binning(o_bins_t* out, const o_draw_t* d, uint32_t width, uint32_t 
  * ---------------------------------------------------------------------------------------------- */
 typedef struct {
   draw3d_kernel_arg_t arg;
+  const uint32_t *tile_xy, *tile_start, *pid_list; /* see o_bins_t */
   const uint8_t* tilebuf;
   const uint8_t* primbuf;
   const uint8_t* texbuf;
@@ -773,10 +795,9 @@ static void render_tile(const o_ctx_t* c, uint32_t L, uint32_t x, uint32_t y, ui
 /* graphics.cpp:715-741 renderPrimitive + gpu_sw.h:34-62 Rasterizer::render (one tile) */
 static void render_one_tile(const o_ctx_t* c, uint32_t cur_tile, uint32_t tile_logsize) {
   const draw3d_kernel_arg_t* a = &c->dev->arg;
-  const rast_tile_header_t* hdr = (const rast_tile_header_t*)c->dev->tilebuf + cur_tile;
-  uint32_t x = (uint32_t)hdr->tile_x << tile_logsize, y = (uint32_t)hdr->tile_y << tile_logsize;
-  uint32_t count = hdr->pids_count, stride = RAS(a, VX_DCR_RASTER_PBUF_STRIDE);
-  const uint32_t* pid_buf = (const uint32_t*)(hdr + 1) + hdr->pids_offset;
+  uint32_t x = (c->dev->tile_xy[cur_tile] >> 16) << tile_logsize, y = (c->dev->tile_xy[cur_tile] & 0xffff) << tile_logsize;
+  uint32_t count = c->dev->tile_start[cur_tile + 1] - c->dev->tile_start[cur_tile], stride = RAS(a, VX_DCR_RASTER_PBUF_STRIDE);
+  const uint32_t* pid_buf = c->dev->pid_list + c->dev->tile_start[cur_tile]; /* == (hdr + 1) + hdr->pids_offset */
   while (count--) {
     uint32_t pid = *pid_buf++;
     const rast_prim_t* prim = (const rast_prim_t*)(c->dev->primbuf + (uint64_t)pid * stride);
@@ -958,7 +979,7 @@ int64_t ref_draw3d_binning(const uint8_t* blob, uint64_t blob_size, uint32_t dra
     *primbuf_size = (uint64_t)b.num_prims * sizeof(rast_prim_t);
     rc = b.num_tiles;
   }
-  free(b.tilebuf); free(b.prims);
+  o_bins_free(&b);
   o_free(&t);
   return rc;
 }
@@ -983,21 +1004,22 @@ int ref_draw3d_render(const uint8_t* blob, uint64_t blob_size, uint32_t width, u
     o_bins_t b;
     double t0;
     o_binning(&b, dc, width, height, tile_logsize);
-    if (b.num_tiles == 0) { free(b.tilebuf); free(b.prims); continue; } /* main.cpp:190-191 */
+    if (b.num_tiles == 0) { o_bins_free(&b); continue; } /* main.cpp:190-191 */
     if (dc->st.texture_enabled) {
       uint32_t k;
       for (k = 0; k < t.nt; ++k)
         if (t.texs[k].id == dc->texture_id) tex = &t.texs[k];
-      if (!tex) { free(b.tilebuf); free(b.prims); o_free(&t); free(dev.zbuf); free(dev.cbuf); return -3; }
+      if (!tex) { o_bins_free(&b); o_free(&t); free(dev.zbuf); free(dev.cbuf); return -3; }
       dev.texbuf = tex->pixels;
     }
     program_draw(&dev.arg, &dc->st, tex, b.num_tiles, width, height);
     dev.tilebuf = b.tilebuf;
+    dev.tile_xy = b.tile_xy; dev.tile_start = b.tile_start; dev.pid_list = b.pid_list;
     dev.primbuf = (const uint8_t*)b.prims;
     t0 = now_s();
     run_kernel(&dev, tile_logsize, num_threads);
     ksec += now_s() - t0;
-    free(b.tilebuf); free(b.prims);
+    o_bins_free(&b);
   }
   if (cbuf_out) memcpy(cbuf_out, dev.cbuf, npix * 4);
   if (zbuf_out) memcpy(zbuf_out, dev.zbuf, npix * 4);

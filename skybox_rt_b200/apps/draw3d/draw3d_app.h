@@ -1,0 +1,70 @@
+/*
+ * draw3d_app.h -- host side of the `draw3d` regression app, as a small C library.
+ *
+ * Follows the reference app tests/regression/draw3d/main.cpp: open -> caps check -> allocate and clear
+ * depth/colour buffers (:461-490) -> per draw call: bin, upload tile/primitive/texture buffers, program
+ * the raster / output-merger / texture DCRs (with the kernel_arg_t mirrors), upload kernel_arg_t,
+ * vx_start, vx_ready_wait (:171-361) -> read the colour buffer back (:380-387).  Everything goes through
+ * the vx_* C ABI (include/vortex.h); nothing here knows about CUDA.
+ *
+ * Two ways to drive it:
+ *   srt_draw3d_render()             the reference's loop verbatim: everything per draw, synchronous;
+ *   srt_draw3d_prepare() + _submit() the same work split so that a frame can be re-submitted with its
+ *                                   buffers resident on the device (what bench.py times as `value`).
+ */
+#ifndef SRT_DRAW3D_APP_H
+#define SRT_DRAW3D_APP_H
+
+#include <stdint.h>
+
+#include "skybox_draw3d.h"
+#include "vortex.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* flags: the reference's command-line switches (main.cpp:110-118) plus this back-end's extension */
+#define SRT_DRAW3D_SW_RAST 0x1 /* -x */
+#define SRT_DRAW3D_SW_OM 0x2   /* -y */
+#define SRT_DRAW3D_SW_TEX 0x4  /* -u */
+#define SRT_DRAW3D_WIDE_TILES 0x8 /* 32-bit tile headers (needed beyond ~64 K tile-primitive pairs) */
+
+typedef struct srt_draw3d srt_draw3d_t;
+
+typedef struct {
+  uint32_t draws_submitted;      /* draws with at least one tile                                  */
+  uint64_t prims, tiles, tile_prims; /* totals over the submitted draws                          */
+  uint64_t h2d_bytes, d2h_bytes; /* bytes moved by the last render / prepare / read              */
+  double bin_ms, upload_ms, run_ms; /* host wall clock of the last render() by phase             */
+} srt_draw3d_stats_t;
+
+/* rank / num_ranks: this process renders the tile rows with (tile_y % num_ranks) == rank; 0,1 = all. */
+int srt_draw3d_open(vx_device_h device, uint32_t width, uint32_t height, uint32_t flags, uint32_t rank,
+                    uint32_t num_ranks, srt_draw3d_t** out);
+void srt_draw3d_close(srt_draw3d_t* r);
+
+/* Host upload of the clear values 0xff000000 / 0xffffffff (main.cpp:45-46, :478-490). */
+int srt_draw3d_clear(srt_draw3d_t* r);
+
+/* The reference's render(): draws [start_draw, end_draw] of the trace, each one binned, uploaded,
+ * started and waited for in turn. */
+int srt_draw3d_render(srt_draw3d_t* r, const srt_trace_t* trace, uint32_t start_draw, uint32_t end_draw);
+
+/* Bin and upload every draw of the trace once and keep the buffers on the device. */
+int srt_draw3d_prepare(srt_draw3d_t* r, const srt_trace_t* trace);
+/* Re-issue the prepared draws: DCR writes + vx_start per draw, no host<->device traffic, no waiting
+ * (call vx_ready_wait afterwards).  `stats` != 0 turns the fragment counters on. */
+int srt_draw3d_submit(srt_draw3d_t* r);
+
+/* Colour (and optionally depth) buffer read-back; width*height u32 each, row 0 = framebuffer row 0. */
+int srt_draw3d_read(srt_draw3d_t* r, uint32_t* cbuf, uint32_t* zbuf);
+
+const srt_draw3d_stats_t* srt_draw3d_stats(const srt_draw3d_t* r);
+vx_buffer_h srt_draw3d_color_buffer(const srt_draw3d_t* r);
+vx_buffer_h srt_draw3d_depth_buffer(const srt_draw3d_t* r);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

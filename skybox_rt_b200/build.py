@@ -95,7 +95,19 @@ def build(force=False, verbose=False):
         if force or _stale(exe, app_src + headers + [vx_so, host_so]):
             _run([CC, "-O2", "-ffp-contract=off", "-Wall", "-Wextra", "-I", INC, "-o", exe] + app_src +
                  ["-L", LIB, "-lvortex", "-lskybox_rt_host", "-lz", "-lm", "-Wl,-rpath,$ORIGIN/../lib"], verbose)
-    return {"vortex": vx_so, "host": host_so}
+    # 4. the draw3d app: its host flow as a library (ctypes-loadable) and the command-line program
+    d3_dir = os.path.join(PKG, "apps", "draw3d")
+    d3_lib_src = [os.path.join(d3_dir, "draw3d_app.c")]
+    d3_so = os.path.join(LIB, "libdraw3d_app.so")
+    link = ["-L", LIB, "-lvortex", "-lskybox_rt_host", "-lz", "-lm"]
+    if force or _stale(d3_so, d3_lib_src + headers + [os.path.join(d3_dir, "draw3d_app.h"), vx_so, host_so]):
+        _run([CC] + HOST_CFLAGS + ["-shared", "-o", d3_so] + d3_lib_src + link + ["-Wl,-rpath,$ORIGIN"], verbose)
+    exe = os.path.join(BIN, "draw3d")
+    d3_src = d3_lib_src + [os.path.join(d3_dir, "main.c"), os.path.join(PKG, "apps", "raytrace", "png_io.c")]
+    if force or _stale(exe, d3_src + headers + [vx_so, host_so]):
+        _run([CC, "-O2", "-ffp-contract=off", "-Wall", "-Wextra", "-I", INC, "-o", exe] + d3_src + link +
+             ["-Wl,-rpath,$ORIGIN/../lib"], verbose)
+    return {"vortex": vx_so, "host": host_so, "draw3d": d3_so}
 
 
 if __name__ == "__main__":

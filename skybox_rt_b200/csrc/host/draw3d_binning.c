@@ -145,6 +145,14 @@ static int setup_prim(const srt_drawcall_t* draw, const srt_primitive_t* tri, co
 
 int srt_draw3d_binning(const srt_drawcall_t* draw, uint32_t width, uint32_t height, uint32_t L, uint32_t format,
                        srt_binning_t* out) {
+  return srt_draw3d_binning_rank(draw, width, height, L, format, 0, 1, out);
+}
+
+/* Multi-GPU: tile rows are dealt round-robin, rank r keeps the tiles with tile_y % num_ranks == r
+ * (tiles are disjoint by construction, gfxutil.cpp:237-250; the reference strides tiles over its own
+ * cores the same way, gpu_sw.h:38).  primbuf is the full one on every rank, so pids mean the same. */
+int srt_draw3d_binning_rank(const srt_drawcall_t* draw, uint32_t width, uint32_t height, uint32_t L, uint32_t format,
+                            uint32_t rank, uint32_t num_ranks, srt_binning_t* out) {
   viewport_xf_t xf;
   uint32_t tiles_x, tiles_y, n, num_prims = 0, num_tiles = 0, tx, ty;
   uint64_t total = 0, ngrid, g;
@@ -155,7 +163,7 @@ int srt_draw3d_binning(const srt_drawcall_t* draw, uint32_t width, uint32_t heig
   size_t hdr_size = format == SRT_TILEBUF_WIDE ? sizeof(srt_tile_header_wide_t) : sizeof(rast_tile_header_t);
   int rc = -1;
   if (!draw || !out || width == 0 || height == 0 || L < 1 || L > 8 || width > 32768 || height > 32768 ||
-      (format != SRT_TILEBUF_REFERENCE && format != SRT_TILEBUF_WIDE))
+      (format != SRT_TILEBUF_REFERENCE && format != SRT_TILEBUF_WIDE) || num_ranks == 0 || rank >= num_ranks)
     return -1;
   memset(out, 0, sizeof(*out));
   xf = make_xf(width, height, draw->viewport.near_, draw->viewport.far_);
@@ -172,7 +180,8 @@ int srt_draw3d_binning(const srt_drawcall_t* draw, uint32_t width, uint32_t heig
     if (!setup_prim(draw, &draw->primitives[n], &xf, width, height, L, tiles_x, tiles_y, &prims[num_prims], &rects[num_prims]))
       continue;
     for (tx = rects[num_prims].tx0; tx < rects[num_prims].tx1; ++tx)
-      for (ty = rects[num_prims].ty0; ty < rects[num_prims].ty1; ++ty) ++count[(uint64_t)tx * tiles_y + ty];
+      for (ty = rects[num_prims].ty0; ty < rects[num_prims].ty1; ++ty)
+        if (ty % num_ranks == rank) ++count[(uint64_t)tx * tiles_y + ty];
     ++num_prims;
   }
   /* exclusive scan -> start of every tile's id list */
@@ -210,7 +219,8 @@ int srt_draw3d_binning(const srt_drawcall_t* draw, uint32_t width, uint32_t heig
     /* pass 2: fill, primitives in submission order */
     for (n = 0; n < num_prims; ++n)
       for (tx = rects[n].tx0; tx < rects[n].tx1; ++tx)
-        for (ty = rects[n].ty0; ty < rects[n].ty1; ++ty) pids[cursor[(uint64_t)tx * tiles_y + ty]++] = n;
+        for (ty = rects[n].ty0; ty < rects[n].ty1; ++ty)
+          if (ty % num_ranks == rank) pids[cursor[(uint64_t)tx * tiles_y + ty]++] = n;
   }
   out->tilebuf = tilebuf; tilebuf = NULL;
   out->tilebuf_size = num_tiles * hdr_size + total * 4;

@@ -124,6 +124,10 @@ const srt_texture_t* srt_trace_texture(const srt_trace_t* t, uint32_t id) {
   return NULL;
 }
 
+const srt_drawcall_t* srt_drawcall_at(const srt_trace_t* t, uint32_t index) {
+  return (t && index < t->num_drawcalls) ? &t->drawcalls[index] : NULL;
+}
+
 /* Format::GetInfo(format).BytePerPixel for the formats the texture unit decodes (format.hpp) */
 uint32_t srt_format_bpp(uint32_t format) {
   switch (format) {

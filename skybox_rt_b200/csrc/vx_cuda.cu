@@ -312,9 +312,10 @@ int vx_dcr_write(vx_device_h hdevice, uint32_t addr, uint32_t value) {
     return -1;
   }
   vx_device* dev = as_dev(hdevice);
-  // the reference blocks until the previous run completes (simx/vortex.cpp:211-218)
-  cudaSetDevice(dev->cuda_dev);
-  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  // The reference blocks here until the previous run completes (simx/vortex.cpp:211-218) because its
+  // units read DCRs while they run.  This back-end latches every DCR it uses into the launch parameters
+  // at vx_start, so a write cannot reach a run in flight and there is nothing to wait for: draws of one
+  // frame queue back to back on the stream.
   dev->dcrs[addr] = value;
   return 0;
 }

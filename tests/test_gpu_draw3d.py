@@ -1,0 +1,145 @@
+"""GPU parity tests of the raster path: the sm_100a tile kernel, reached through the vx_* C ABI by the C
+host flow of apps/draw3d, against the reference's golden images and the CPU oracle.  Bar: bit-exact
+colour AND depth/stencil words (the reference's own compare tolerates 1/255, draw3d/main.cpp:507)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import _oracle_draw3d as od
+
+pytestmark = pytest.mark.gpu
+
+GOLDENS = od.goldens()
+NAMES = od.trace_names()
+ALL_SW = 7  # -x -y -u
+
+
+@pytest.fixture(scope="module")
+def d3(native):
+    from skybox_rt_b200 import draw3d
+    from skybox_rt_b200 import vortex
+    vortex.lib()  # raises if libvortex.so is missing: no fallback
+    return draw3d
+
+
+def checker():
+    """The compiled reference when it travelled with the snapshot, else the restatement."""
+    return od.reference() or od.oracle()
+
+
+@pytest.mark.parametrize("name,size,path", GOLDENS, ids=[f"{n}@{s}" for n, s, _ in GOLDENS])
+def test_reference_goldens_bit_exact(d3, name, size, path):
+    with d3.Draw3D(size, size, flags=ALL_SW) as app:
+        fb = app.frame(d3.Trace(blob=od.trace_blob(name)))
+    gold = od.golden_framebuffer(path)
+    assert int((fb != gold).sum()) == 0
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("w,h", [(64, 64), (200, 120), (333, 517), (1000, 700)])
+def test_colour_and_depth_match_oracle(d3, name, w, h):
+    blob = od.trace_blob(name)
+    with d3.Draw3D(w, h, flags=ALL_SW) as app:
+        fb, zb = app.frame(d3.Trace(blob=blob), depth=True)
+    fo, zo, _ = od.render(checker(), blob, w, h, threads=8)
+    assert int((fb != fo).sum()) == 0, (name, w, h)
+    assert int((zb != zo).sum()) == 0, (name, w, h)
+
+
+@pytest.mark.parametrize("name", ["vase", "mouse", "tekkaman"])
+def test_hardware_unit_path_equals_software_path(d3, name):
+    # without -x -y -u the units read the device DCR file instead of the kernel_arg mirrors
+    t = d3.Trace(blob=od.trace_blob(name))
+    with d3.Draw3D(256, 192, flags=0) as app:
+        hw = app.frame(t, depth=True)
+    with d3.Draw3D(256, 192, flags=ALL_SW) as app:
+        sw = app.frame(t, depth=True)
+    assert np.array_equal(hw[0], sw[0]) and np.array_equal(hw[1], sw[1])
+
+
+@pytest.mark.parametrize("name", ["evilskull", "polybump"])
+def test_prepared_resubmission_equals_per_draw_render(d3, name):
+    t = d3.Trace(blob=od.trace_blob(name))
+    with d3.Draw3D(400, 300, flags=ALL_SW | d3.WIDE_TILES) as app:
+        ref = app.frame(t, depth=True)
+        app.prepare(t)
+        for _ in range(2):  # the same prepared frame twice: clear, submit all draws back to back, wait
+            app.clear()
+            app.submit()
+            app.wait()
+            got = app.read(depth=True)
+            assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1])
+
+
+@pytest.mark.parametrize("name,size", [("mouse", 2048), ("vase", 4096), ("carnival", 4096)])
+def test_full_size_frames_match_oracle(d3, name, size):
+    """BASELINE-sized frames (wide tile headers).  The oracle walks its own tile lists, so it stays a
+    valid checker where the reference's 16-bit tile header format ends."""
+    blob = od.trace_blob(name)
+    with d3.Draw3D(size, size, flags=ALL_SW | d3.WIDE_TILES) as app:
+        fb, zb = app.frame(d3.Trace(blob=blob), depth=True)
+    fo, zo, _ = od.render(od.oracle(), blob, size, size, threads=os.cpu_count() or 8)
+    assert int((fb != fo).sum()) == 0 and int((zb != zo).sum()) == 0
+
+
+def test_rank_strips_compose_the_single_gpu_frame(d3):
+    blob = od.trace_blob("evilskull")
+    t = d3.Trace(blob=blob)
+    w, h, n = 320, 272, 3
+    with d3.Draw3D(w, h, flags=ALL_SW) as app:
+        full, zfull = app.frame(t, depth=True)
+    out = np.full((h, w), 0xFF000000, np.uint32)
+    for r in range(n):
+        with d3.Draw3D(w, h, flags=ALL_SW, rank=r, num_ranks=n) as app:
+            part = app.frame(t)
+        rows = [y for y in range(h) if (y // 32) % n == r]
+        out[rows] = part[rows]
+        other = [y for y in range(h) if (y // 32) % n != r]
+        assert (part[other] == 0xFF000000).all()  # a rank never touches another rank's tile rows
+    assert np.array_equal(out, full)
+
+
+def test_fragment_counters(d3):
+    from skybox_rt_b200 import vortex as vx
+    t = d3.Trace(blob=od.trace_blob("triangle"))
+    with d3.Draw3D(128, 128, flags=ALL_SW) as app:
+        app.dev.dcr_write(vx.VX_DCR_RT_STATS, 1)
+        fb = app.frame(t)
+        frags = app.dev.mpm_query(d3.VX_CSR_RASTER_FRAGMENTS)
+        tiles = app.dev.mpm_query(d3.VX_CSR_RASTER_TILES)
+    # one opaque triangle, no depth test: every shaded fragment is a written pixel
+    assert frags == int((fb != 0xFF000000).sum()) and tiles == 16
+
+
+def test_bad_state_is_refused_not_rendered(d3):
+    from skybox_rt_b200 import vortex as vx
+    t = d3.Trace(blob=od.trace_blob("triangle"))
+    with d3.Draw3D(64, 64, flags=0) as app:
+        app.prepare(t)
+        app.submit()
+        app.wait()
+        # an arguments buffer that is too small for kernel_arg_t must fail vx_start (callbacks.inc conventions)
+        small = app.dev.upload(np.zeros(16, np.uint8))
+        img = np.zeros(4, np.uint64)
+        img[0], img[1], img[2], img[3] = 0x80000000, 0x80000040, 0x5452584F42594B53, 2 | (1 << 32)
+        k = app.dev.upload_kernel(img.tobytes())
+        with pytest.raises(vx.VortexError):
+            app.dev.start(k, small)
+
+
+def test_draw3d_app_compares_against_reference_golden(native, tmp_path):
+    """The C program end to end: trace file in, PNG out, exit code = mismatching pixels (main.cpp:505-514)."""
+    from PIL import Image
+    exe = os.path.join(os.path.dirname(native["vortex"]), "..", "bin", "draw3d")
+    gold = np.load(os.path.join(od.GOLDEN_DIR, "vase_ref_128.npy"))
+    rgba = np.stack([(gold >> 16) & 255, (gold >> 8) & 255, gold & 255, gold >> 24], -1).astype(np.uint8)
+    ref_png, out_png = str(tmp_path / "vase_ref_128.png"), str(tmp_path / "out.png")
+    Image.fromarray(rgba, "RGBA").save(ref_png)
+    p = subprocess.run([exe, "-t", os.path.join(od.GOLDEN_DIR, "vase.trc.gz"), "-w", "128", "-h", "128", "-x", "-y",
+                        "-u", "-o", out_png, "-r", ref_png], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "PASSED!" in p.stdout
+    got = np.asarray(Image.open(out_png).convert("RGBA"))
+    assert np.array_equal(got, rgba)
