@@ -48,7 +48,10 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + ["draw3d"],
+                    help="c1..c5: the RT configs of BASELINE.json; draw3d: the raster path (bench_draw3d.py)")
+    ap.add_argument("--trace", default="mouse", help="draw3d: which reference trace (tests/golden/raster/<name>.trc.gz)")
+    ap.add_argument("--size", type=int, default=4096, help="draw3d: render target is size x size")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel, 2 wide while-while")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
@@ -365,6 +368,13 @@ def load_peaks():
 
 def main():
     args = parse()
+    if args.workload == "draw3d":
+        import bench_draw3d
+        if args.impl == "reference":
+            bench_draw3d.reference_arm(args)
+        else:
+            bench_draw3d.native_arm(args, ClockSampler, load_peaks)
+        return
     wl = dict(WORKLOADS[args.workload])
     if args.mode is not None and wl["mode"] != 3:
         wl["mode"] = args.mode

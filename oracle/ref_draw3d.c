@@ -692,6 +692,10 @@ static uint32_t mul_shift24_u8(int32_t fx, uint32_t k) { /* :61-71: (data * k) >
   return (((uint32_t)fx * k) >> 24) & 0xff;
 }
 
+/* test-side instrumentation (not in the reference): fragments handed to the output merger */
+static int g_count_frags = 0;
+static volatile uint64_t g_frags = 0;
+
 static void shade_quad(const o_ctx_t* c, uint32_t pos_mask, const int32_t bc[4][3], uint32_t pid) {
   const draw3d_kernel_arg_t* a = &c->dev->arg;
   const rast_prim_t* prim = (const rast_prim_t*)(c->dev->primbuf + (uint64_t)pid * sizeof(rast_prim_t));
@@ -700,6 +704,7 @@ static void shade_quad(const o_ctx_t* c, uint32_t pos_mask, const int32_t bc[4][
   uint32_t qx = (pos_mask >> 4) & ((1 << (VX_RASTER_DIM_BITS - 1)) - 1);
   uint32_t qy = (pos_mask >> (4 + (VX_RASTER_DIM_BITS - 1))) & ((1 << (VX_RASTER_DIM_BITS - 1)) - 1);
   int i;
+  if (g_count_frags) __sync_fetch_and_add(&g_frags, (uint64_t)__builtin_popcount(mask));
   for (i = 0; i < 4; ++i) {
     int32_t z = 0, r = 1 << 24, g = 1 << 24, b = 1 << 24, al = 1 << 24, u = 0, v = 0, dx, dy; /* DEFAULTS :15-22 */
     uint32_t out;
@@ -1027,6 +1032,18 @@ int ref_draw3d_render(const uint8_t* blob, uint64_t blob_size, uint32_t width, u
   free(dev.zbuf); free(dev.cbuf);
   o_free(&t);
   return 0;
+}
+
+/* Fragments one frame sends to the output merger (the unit bench.py's draw3d metric counts). */
+uint64_t ref_draw3d_count_fragments(const uint8_t* blob, uint64_t blob_size, uint32_t width, uint32_t height,
+                                    uint32_t num_threads) {
+  uint64_t n;
+  g_frags = 0;
+  g_count_frags = 1;
+  if (ref_draw3d_render(blob, blob_size, width, height, num_threads, RASTER_TILE_LOGSIZE, NULL, NULL, NULL) != 0) g_frags = 0;
+  g_count_frags = 0;
+  n = g_frags;
+  return n;
 }
 
 /* ---- sub-stage probes ------------------------------------------------------------------------- */

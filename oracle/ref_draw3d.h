@@ -38,6 +38,8 @@ int64_t ref_draw3d_binning(const uint8_t* blob, uint64_t blob_size, uint32_t dra
                            uint32_t height, uint32_t tile_logsize, uint8_t* tilebuf_out,
                            uint64_t* tilebuf_size, uint8_t* primbuf_out, uint64_t* primbuf_size);
 
+uint64_t ref_draw3d_count_fragments(const uint8_t* blob, uint64_t blob_size, uint32_t width, uint32_t height,
+                                    uint32_t num_threads);
 uint32_t ref_draw3d_kernel_arg_size(void);
 uint32_t ref_draw3d_prim_size(void);
 

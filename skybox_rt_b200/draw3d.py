@@ -186,6 +186,15 @@ class Draw3D:
         self._ck(app_lib().srt_draw3d_read(self.h, cp, z.ctypes.data if depth else None), "srt_draw3d_read")
         return (c, z) if depth else c
 
+    def buffer_addresses(self):
+        """(colour, depth) device addresses as vx_mem_address reports them (CUDA device pointers)."""
+        out = []
+        for fn in (app_lib().srt_draw3d_color_buffer, app_lib().srt_draw3d_depth_buffer):
+            a = C.c_uint64()
+            self._ck(vx.lib().vx_mem_address(fn(self.h), C.byref(a)), "vx_mem_address")
+            out.append(a.value)
+        return tuple(out)
+
     def stats(self):
         s = app_lib().srt_draw3d_stats(self.h).contents
         return {k: getattr(s, k) for k, _ in Stats._fields_}

@@ -110,7 +110,7 @@ def test_fragment_counters(d3):
         frags = app.dev.mpm_query(d3.VX_CSR_RASTER_FRAGMENTS)
         tiles = app.dev.mpm_query(d3.VX_CSR_RASTER_TILES)
     # one opaque triangle, no depth test: every shaded fragment is a written pixel
-    assert frags == int((fb != 0xFF000000).sum()) and tiles == 16
+    assert frags == int((fb != 0xFF000000).sum()) and tiles == t.binning(0, 128, 128)[0]
 
 
 def test_bad_state_is_refused_not_rendered(d3):
