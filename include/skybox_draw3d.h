@@ -237,6 +237,7 @@ typedef struct {
   uint32_t reserved;
 } srt_tile_header_wide_t; /* 16 B */
 #define VX_DCR_RASTER_EXT_TBUF_FORMAT 0x804 /* back-end DCR (outside the reference's ranges); 0 after open */
+#define VX_DCR_RASTER_EXT_GENERIC 0x805     /* 1 = never use the state-specialised kernels (A/B testing)   */
 
 typedef struct {
   uint8_t* tilebuf;   uint64_t tilebuf_size;

@@ -18,6 +18,12 @@ extern "C" {
 /* The CUDA stream vx_start launches on and vx_copy_* are ordered with (owned by the device). */
 int vx_cuda_stream(vx_device_h hdevice, void** stream);
 
+/* Page-lock a host range the app reuses for vx_copy_to_dev / vx_copy_from_dev (cudaHostRegister), so
+ * those copies run as direct DMA at link rate instead of through the driver's staging buffer.  Optional:
+ * the copies work on any host pointer.  The range must stay mapped until vx_cuda_host_unregister. */
+int vx_cuda_host_register(vx_device_h hdevice, void* ptr, uint64_t size);
+int vx_cuda_host_unregister(vx_device_h hdevice, void* ptr);
+
 /* CUDA device ordinal the handle was opened on. */
 int vx_cuda_device(vx_device_h hdevice, int* ordinal);
 

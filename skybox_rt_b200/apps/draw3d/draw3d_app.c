@@ -2,6 +2,7 @@
  * draw3d_app.c -- host side of the draw3d regression app (plain C over the vx_* ABI).
  * See draw3d_app.h; line references are to the reference's tests/regression/draw3d/main.cpp.
  */
+#define _POSIX_C_SOURCE 200809L
 #include "draw3d_app.h"
 
 #include <stdio.h>
@@ -10,6 +11,7 @@
 #include <time.h>
 
 #include "skybox_rt.h"
+#include "vortex_cuda.h"
 
 #define CHECK(expr)                                                \
   do {                                                             \
@@ -38,6 +40,10 @@ struct srt_draw3d {
   /* prepare()/submit(): one slot per draw call, resident */
   draw_slot_t* slots;
   uint32_t num_slots;
+  /* clear values kept in one staging buffer per target for the life of the app (the reference builds a
+   * fresh std::vector per run, main.cpp:480-489); page-locked when the back-end offers it */
+  uint32_t *clear_z, *clear_c;
+  int clear_z_pinned, clear_c_pinned;
   srt_draw3d_stats_t stats;
 };
 
@@ -216,6 +222,16 @@ int srt_draw3d_open(vx_device_h device, uint32_t width, uint32_t height, uint32_
     srt_draw3d_close(r);
     return -1;
   }
+  {
+    uint64_t i;
+    if (posix_memalign((void**)&r->clear_z, 4096, (r->zbuf_size + 4095) & ~4095ull) != 0) r->clear_z = NULL;
+    if (posix_memalign((void**)&r->clear_c, 4096, (r->cbuf_size + 4095) & ~4095ull) != 0) r->clear_c = NULL;
+    if (!r->clear_z || !r->clear_c) { srt_draw3d_close(r); return -1; }
+    for (i = 0; i < r->zbuf_size / 4; ++i) r->clear_z[i] = 0xffffffffu; /* clear_depth, main.cpp:46 */
+    for (i = 0; i < r->cbuf_size / 4; ++i) r->clear_c[i] = 0xff000000u; /* clear_color, main.cpp:45 */
+    r->clear_z_pinned = vx_cuda_host_register(device, r->clear_z, r->zbuf_size) == 0;
+    r->clear_c_pinned = vx_cuda_host_register(device, r->clear_c, r->cbuf_size) == 0;
+  }
   /* main.cpp:493-496 */
   r->kernel_arg.log_num_tasks = log2ceil_u32((uint32_t)(num_cores * num_warps * num_threads));
   r->kernel_arg.sw_tex = (flags & SRT_DRAW3D_SW_TEX) != 0;
@@ -241,6 +257,10 @@ static void free_slots(srt_draw3d_t* r) {
 void srt_draw3d_close(srt_draw3d_t* r) { /* cleanup(), main.cpp:137-146 (the device stays the caller's) */
   if (!r) return;
   free_slots(r);
+  if (r->clear_z_pinned) vx_cuda_host_unregister(r->device, r->clear_z);
+  if (r->clear_c_pinned) vx_cuda_host_unregister(r->device, r->clear_c);
+  free(r->clear_z);
+  free(r->clear_c);
   vx_mem_free(r->depth_buffer);
   vx_mem_free(r->color_buffer);
   vx_mem_free(r->tex_buffer);
@@ -252,16 +272,8 @@ void srt_draw3d_close(srt_draw3d_t* r) { /* cleanup(), main.cpp:137-146 (the dev
 }
 
 int srt_draw3d_clear(srt_draw3d_t* r) { /* main.cpp:478-490 */
-  uint64_t i, n = r->zbuf_size / 4;
-  uint32_t* staging = (uint32_t*)malloc(r->zbuf_size > r->cbuf_size ? r->zbuf_size : r->cbuf_size);
-  int rc;
-  if (!staging) return -1;
-  for (i = 0; i < n; ++i) staging[i] = 0xffffffffu;
-  rc = vx_copy_to_dev(r->depth_buffer, staging, 0, r->zbuf_size);
-  n = r->cbuf_size / 4;
-  for (i = 0; i < n; ++i) staging[i] = 0xff000000u;
-  if (rc == 0) rc = vx_copy_to_dev(r->color_buffer, staging, 0, r->cbuf_size);
-  free(staging);
+  int rc = vx_copy_to_dev(r->depth_buffer, r->clear_z, 0, r->zbuf_size);
+  if (rc == 0) rc = vx_copy_to_dev(r->color_buffer, r->clear_c, 0, r->cbuf_size);
   r->stats.h2d_bytes = r->zbuf_size + r->cbuf_size;
   return rc;
 }

@@ -196,16 +196,41 @@ int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg) {
     P.texbuf = tb + mip0;
   }
 
+  // pick the instantiation whose compile-time state equals the decoded state (raster_tile.cuh)
+  int texk = 0, blendk = 0;
+  if (P.sh_tex) {
+    texk = 1;
+    if (P.tex_filter == VX_TEX_FILTER_BILINEAR && P.tex_wrapu == VX_TEX_WRAP_REPEAT && P.tex_wrapv == VX_TEX_WRAP_REPEAT) {
+      if (P.tex_format == VX_TEX_FORMAT_A8R8G8B8) texk = 2;
+      else if (P.tex_format == VX_TEX_FORMAT_R5G6B5) texk = 3;
+      else if (P.tex_format == VX_TEX_FORMAT_A8L8) texk = 4;
+    }
+  }
+  if (P.blend_enabled) {
+    blendk = 1;
+    if (P.bl_mode_rgb == VX_OM_BLEND_MODE_ADD && P.bl_mode_a == VX_OM_BLEND_MODE_ADD && P.bl_src_rgb == VX_OM_BLEND_FUNC_SRC_A &&
+        P.bl_src_a == VX_OM_BLEND_FUNC_SRC_A && P.bl_dst_rgb == VX_OM_BLEND_FUNC_ONE_MINUS_SRC_A &&
+        P.bl_dst_a == VX_OM_BLEND_FUNC_ONE_MINUS_SRC_A)
+      blendk = 2;
+  }
+  if (dev_dcr(dev, VX_DCR_RASTER_EXT_GENERIC) != 0) {  // A/B switch: always the generic instantiation
+    texk = texk ? 1 : 0;
+    blendk = blendk ? 1 : 0;
+  }
   const bool stats = dev_dcr(dev, VX_DCR_RT_STATS) != 0;
   if (stats) {
     if (!st->d_counters) VX_CUDA_OK(cudaMalloc(&st->d_counters, 2 * sizeof(unsigned long long)));
     VX_CUDA_OK(cudaMemsetAsync(st->d_counters, 0, 2 * sizeof(unsigned long long), dev->stream));
     P.counters = st->d_counters;
     st->counters_live = true;
-    raster_tile_kernel<true><<<P.num_tiles, kRasterThreads, 0, dev->stream>>>(P);
-  } else {
-    raster_tile_kernel<false><<<P.num_tiles, kRasterThreads, 0, dev->stream>>>(P);
   }
+  using kernel_t = void (*)(const RasterParams);
+#define SRT_ROW(S, T) {raster_tile_kernel<S, T, 0>, raster_tile_kernel<S, T, 1>, raster_tile_kernel<S, T, 2>}
+  static const kernel_t table[2][5][3] = {
+      {SRT_ROW(false, 0), SRT_ROW(false, 1), SRT_ROW(false, 2), SRT_ROW(false, 3), SRT_ROW(false, 4)},
+      {SRT_ROW(true, 0), SRT_ROW(true, 1), SRT_ROW(true, 2), SRT_ROW(true, 3), SRT_ROW(true, 4)}};
+#undef SRT_ROW
+  table[stats ? 1 : 0][texk][blendk]<<<P.num_tiles, kRasterThreads, 0, dev->stream>>>(P);
   VX_CUDA_OK(cudaGetLastError());
   dev->last_launches = 1;
   return 0;

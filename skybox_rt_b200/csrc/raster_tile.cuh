@@ -56,7 +56,7 @@ struct RasterParams {
 };
 
 constexpr int kRasterThreads = 256;
-constexpr int kPrimChunk = 16;  // primitives staged per round: 16 * 120 B = 1920 B of shared memory
+constexpr int kPrimChunk = 48;  // primitives staged per round: 48 * 120 B = 5760 B of shared memory
 
 __device__ __forceinline__ int32_t x86_cvtt(float f) {
   return (f >= -2147483648.0f && f < 2147483648.0f) ? (int32_t)f : (int32_t)0x80000000;
@@ -134,12 +134,14 @@ __device__ __forceinline__ uint32_t fetch_texel(const uint8_t* base, uint32_t of
   return __ldg(base + offset);
 }
 
-__device__ __forceinline__ uint32_t tex_sample(const RasterParams& P, int32_t u, int32_t v) {
-  const uint32_t lw = P.tex_log_width, lh = P.tex_log_height, fmt = P.tex_format;
-  if (P.tex_filter == VX_TEX_FILTER_BILINEAR) {
+// fmt / filter / wrapu / wrapv are passed separately so that a specialised kernel can hand in constants
+__device__ __forceinline__ uint32_t tex_sample(const RasterParams& P, int32_t u, int32_t v, uint32_t fmt, uint32_t filter,
+                                               uint32_t wrapu, uint32_t wrapv) {
+  const uint32_t lw = P.tex_log_width, lh = P.tex_log_height;
+  if (filter == VX_TEX_FILTER_BILINEAR) {
     const int32_t dx = (1 << (kTexFrac - 1)) >> lw, dy = (1 << (kTexFrac - 1)) >> lh;
-    const uint32_t u0 = tex_wrap(u - dx, P.tex_wrapu), u1 = tex_wrap(u + dx, P.tex_wrapu);
-    const uint32_t v0 = tex_wrap(v - dy, P.tex_wrapv), v1 = tex_wrap(v + dy, P.tex_wrapv);
+    const uint32_t u0 = tex_wrap(u - dx, wrapu), u1 = tex_wrap(u + dx, wrapu);
+    const uint32_t v0 = tex_wrap(v - dy, wrapv), v1 = tex_wrap(v + dy, wrapv);
     const uint32_t shift_u = kTexFrac - lw, shift_v = kTexFrac - lh;
     const uint32_t x0s = (u0 << 8) >> shift_u, y0s = (v0 << 8) >> shift_v;
     const uint32_t x0 = x0s >> 8, y0 = y0s >> 8, x1 = u1 >> shift_u, y1 = v1 >> shift_v;
@@ -157,7 +159,7 @@ __device__ __forceinline__ uint32_t tex_sample(const RasterParams& P, int32_t u,
     const uint32_t ch = lerp8888(lerp8888(c0h, c1h, alpha), lerp8888(c2h, c3h, alpha), beta);
     return (ch << 8) | cl;
   }
-  const uint32_t uu = tex_wrap(u, P.tex_wrapu), vv = tex_wrap(v, P.tex_wrapv);
+  const uint32_t uu = tex_wrap(u, wrapu), vv = tex_wrap(v, wrapv);
   const uint32_t x = uu >> (kTexFrac - lw), y = vv >> (kTexFrac - lh);
   uint32_t cl, ch;
   unpack8888(fmt, fetch_texel(P.texbuf, x + (y << lw), fmt), cl, ch);
@@ -280,11 +282,12 @@ __device__ __forceinline__ uint32_t blend_mode(uint32_t mode, uint32_t logic_op,
   }
 }
 
-__device__ __forceinline__ uint32_t blend(const RasterParams& P, uint32_t src, uint32_t dst) {
-  const uint32_t s_rgb = blend_factor(P.bl_src_rgb, src, dst, P.bl_const), s_a = blend_factor(P.bl_src_a, src, dst, P.bl_const);
-  const uint32_t d_rgb = blend_factor(P.bl_dst_rgb, src, dst, P.bl_const), d_a = blend_factor(P.bl_dst_a, src, dst, P.bl_const);
-  const uint32_t rgb = blend_mode(P.bl_mode_rgb, P.logic_op, src, dst, s_rgb, d_rgb);
-  const uint32_t a = blend_mode(P.bl_mode_a, P.logic_op, src, dst, s_a, d_a);
+struct BlendState { uint32_t mode_rgb, mode_a, src_rgb, src_a, dst_rgb, dst_a; };
+__device__ __forceinline__ uint32_t blend(const RasterParams& P, const BlendState& B, uint32_t src, uint32_t dst) {
+  const uint32_t s_rgb = blend_factor(B.src_rgb, src, dst, P.bl_const), s_a = blend_factor(B.src_a, src, dst, P.bl_const);
+  const uint32_t d_rgb = blend_factor(B.dst_rgb, src, dst, P.bl_const), d_a = blend_factor(B.dst_a, src, dst, P.bl_const);
+  const uint32_t rgb = blend_mode(B.mode_rgb, P.logic_op, src, dst, s_rgb, d_rgb);
+  const uint32_t a = blend_mode(B.mode_a, P.logic_op, src, dst, s_a, d_a);
   return (a & 0xff000000u) | (rgb & 0x00ffffffu);
 }
 
@@ -303,8 +306,29 @@ __device__ __forceinline__ uint32_t mul_u8(int32_t fx, uint32_t k) { return (((u
 // ---------------------------------------------------------------- the tile kernel
 // Thread -> quad: warp w covers the 16x8-pixel block at ((w & 1) * 16, (w >> 1) * 8) of the tile, lane l the
 // quad (l & 7, l >> 3) of the block.  A warp's framebuffer rows are then 64 contiguous bytes.
-template <bool STATS>
+//
+// Specialisation.  All fixed-function state is uniform over a launch; the generic kernel walks it through
+// switch statements per fragment (format decode, blend factors, compare functions).  TEXK / BLENDK select
+// instantiations in which the commonest states are compile-time constants so those switches fold away:
+//   TEXK   0 no texture | 1 any state | 2 A8R8G8B8 | 3 R5G6B5 | 4 A8L8  (2..4: bilinear, repeat/repeat)
+//   BLENDK 0 blending off | 1 any state | 2 SRC_A / ONE_MINUS_SRC_A, ADD (glBlendFunc(SRC_ALPHA, ONE_MINUS_SRC_ALPHA))
+// raster_pipeline.cu picks the instantiation from the decoded state; results are identical by construction
+// (same functions, constant arguments).
+template <bool STATS, int TEXK, int BLENDK>
 __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const RasterParams P) {
+  const uint32_t tex_fmt = TEXK == 2 ? VX_TEX_FORMAT_A8R8G8B8 : TEXK == 3 ? VX_TEX_FORMAT_R5G6B5 : TEXK == 4 ? VX_TEX_FORMAT_A8L8 : P.tex_format;
+  const uint32_t tex_filter = TEXK >= 2 ? VX_TEX_FILTER_BILINEAR : P.tex_filter;
+  const uint32_t tex_wrapu = TEXK >= 2 ? VX_TEX_WRAP_REPEAT : P.tex_wrapu, tex_wrapv = TEXK >= 2 ? VX_TEX_WRAP_REPEAT : P.tex_wrapv;
+  const bool sh_tex = TEXK != 0, blend_enabled = BLENDK != 0;
+  BlendState B;
+  if (BLENDK == 2) {
+    B.mode_rgb = B.mode_a = VX_OM_BLEND_MODE_ADD;
+    B.src_rgb = B.src_a = VX_OM_BLEND_FUNC_SRC_A;
+    B.dst_rgb = B.dst_a = VX_OM_BLEND_FUNC_ONE_MINUS_SRC_A;
+  } else {
+    B.mode_rgb = P.bl_mode_rgb; B.mode_a = P.bl_mode_a; B.src_rgb = P.bl_src_rgb; B.src_a = P.bl_src_a;
+    B.dst_rgb = P.bl_dst_rgb; B.dst_a = P.bl_dst_a;
+  }
   __shared__ int32_t s_prims[kPrimChunk][30];  // rast_prim_t = 30 words
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
@@ -338,7 +362,7 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
   uint32_t col[4] = {0, 0, 0, 0}, ds[4] = {0, 0, 0, 0};
   uint32_t col_dirty = 0, ds_dirty = 0;
   const bool need_ds = P.om_depth_enabled || P.om_stencil_enabled;
-  const bool need_col = P.color_write && (P.color_read || P.blend_enabled);
+  const bool need_col = P.color_write && (P.color_read || blend_enabled);
 #pragma unroll
   for (int p = 0; p < 4; ++p) {
     if (inside & (1u << p)) {
@@ -363,25 +387,34 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
     for (uint32_t k = 0; k < n; ++k) {
       const int32_t* pr = s_prims[k];
       // edges e[i] = (a, b, c) at pr[3i .. 3i+2]; int32 wrap-around arithmetic throughout
-      uint32_t reject = 0;
-      int32_t eq[3];  // edge values at the quad's top-left pixel
+      // renderTile / renderQuad rejection for this quad's ancestors (graphics.cpp:749-753, :805-809):
+      // value at the ancestor's origin + (extent << level) < 0 on any edge.  Levels 5 (tile) and 4 (16x16
+      // block) are the same for all lanes of a warp, so a warp leaves the primitive here without diverging.
+      uint32_t reject = 0, ext[3];
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
         const uint32_t a = (uint32_t)pr[3 * i], b = (uint32_t)pr[3 * i + 1], c = (uint32_t)pr[3 * i + 2];
         const int32_t sa = (int32_t)a, sb = (int32_t)b;
-        // CalcEdgeExtents (graphics.cpp:644-647)
-        const uint32_t ext = (sb >= 0) ? ((sa >= 0) ? a + b : b) : ((sa >= 0) ? a : 0u);
-        // renderTile / renderQuad rejection for this quad's ancestors, tile (32) down to the quad (2)
-        // (graphics.cpp:749-753, :805-809): value at the ancestor's origin + (extent << level) < 0
+        ext[i] = (sb >= 0) ? ((sa >= 0) ? a + b : b) : ((sa >= 0) ? a : 0u);  // CalcEdgeExtents (graphics.cpp:644-647)
 #pragma unroll
-        for (int L = RASTER_TILE_LOGSIZE; L >= 1; --L) {
+        for (int L = RASTER_TILE_LOGSIZE; L >= RASTER_TILE_LOGSIZE - 1; --L) {
           const uint32_t ox = X0 + (lx & ~((1u << L) - 1)), oy = Y0 + (ly & ~((1u << L) - 1));
-          const uint32_t v = a * ox + b * oy + c;
-          reject |= (v + (ext << L)) >> 31;
+          reject |= (a * ox + b * oy + c + (ext[i] << L)) >> 31;
+        }
+      }
+      if (STATS) ++n_tested;
+      if (reject) continue;
+      int32_t eq[3];  // edge values at the quad's top-left pixel
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const uint32_t a = (uint32_t)pr[3 * i], b = (uint32_t)pr[3 * i + 1], c = (uint32_t)pr[3 * i + 2];
+#pragma unroll
+        for (int L = RASTER_TILE_LOGSIZE - 2; L >= 1; --L) {
+          const uint32_t ox = X0 + (lx & ~((1u << L) - 1)), oy = Y0 + (ly & ~((1u << L) - 1));
+          reject |= (a * ox + b * oy + c + (ext[i] << L)) >> 31;
         }
         eq[i] = (int32_t)(a * px + b * py + c);
       }
-      if (STATS) ++n_tested;
       if (reject) continue;
       // PREPARE_QUAD (graphics.cpp:811-830)
       uint32_t mask = 0;
@@ -416,9 +449,9 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
           cr = interp(pr + 12, dx, dy); cg = interp(pr + 15, dx, dy);
           cb = interp(pr + 18, dx, dy); ca = interp(pr + 21, dx, dy);
         }
-        if (P.sh_tex) {
+        if (sh_tex) {
           const int32_t u = interp(pr + 24, dx, dy), v = interp(pr + 27, dx, dy);
-          const uint32_t t = tex_sample(P, u >> 1, v >> 1);  // 8.24 -> 9.23 (kernel.cpp:160-164)
+          const uint32_t t = tex_sample(P, u >> 1, v >> 1, tex_fmt, tex_filter, tex_wrapu, tex_wrapv);  // 8.24 -> 9.23 (kernel.cpp:160-164)
           color = P.sh_modulate ? ((mul_u8(ca, t >> 24) << 24) | (mul_u8(cr, (t >> 16) & 0xff) << 16) |
                                    (mul_u8(cg, (t >> 8) & 0xff) << 8) | mul_u8(cb, t & 0xff))
                                 : t;
@@ -428,7 +461,7 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
         // OutputMerger::write (gpu_sw.h:103-168) on the register copies
         uint32_t ds_new = 0;
         const bool ds_passed = !need_ds || ds_test(P, (uint32_t)z, ds[p], ds_new);
-        if (P.blend_enabled && ds_passed) color = blend(P, color, col[p]);
+        if (blend_enabled && ds_passed) color = blend(P, B, color, col[p]);
         const uint32_t ds_wm = ((P.om_depth_enabled && ds_passed && P.depth_writemask) ? VX_OM_DEPTH_MASK : 0u) |
                                (P.om_stencil_enabled ? (P.stencil_writemask << VX_OM_DEPTH_BITS) : 0u);
         if (ds_wm) {

@@ -378,6 +378,27 @@ int vx_cuda_stream(vx_device_h hdevice, void** stream) {
   return 0;
 }
 
+int vx_cuda_host_register(vx_device_h hdevice, void* ptr, uint64_t size) {
+  if (nullptr == hdevice || nullptr == ptr || 0 == size) return -1;
+  cudaSetDevice(as_dev(hdevice)->cuda_dev);
+  cudaError_t e = cudaHostRegister(ptr, size, cudaHostRegisterDefault);
+  if (e != cudaSuccess) {
+    cudaGetLastError();  // not sticky; the caller simply keeps a pageable buffer
+    return -1;
+  }
+  return 0;
+}
+
+int vx_cuda_host_unregister(vx_device_h hdevice, void* ptr) {
+  if (nullptr == hdevice || nullptr == ptr) return -1;
+  cudaSetDevice(as_dev(hdevice)->cuda_dev);
+  if (cudaHostUnregister(ptr) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  return 0;
+}
+
 int vx_cuda_device(vx_device_h hdevice, int* ordinal) {
   if (nullptr == hdevice || nullptr == ordinal) return -1;
   *ordinal = as_dev(hdevice)->cuda_dev;

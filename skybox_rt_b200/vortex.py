@@ -39,7 +39,7 @@ EXPORTS = [
     "vx_upload_kernel_file", "vx_upload_bytes", "vx_upload_file", "vx_check_occupancy", "vx_dump_perf",
     "vx_dev_init",
 ]
-CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device"]  # include/vortex_cuda.h
+CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx_cuda_host_unregister"]  # include/vortex_cuda.h
 
 _lib = None
 

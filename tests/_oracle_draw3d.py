@@ -101,3 +101,75 @@ def golden_framebuffer(path):
 
 def num_draws(blob):
     return int(np.frombuffer(blob[8:12], np.uint32)[0])
+
+
+# ---------------------------------------------------------------- state mutation (widens what the traces cover)
+STATE_FIELDS = ["color_enabled", "color_format", "color_writemask", "depth_test", "depth_writemask", "depth_format",
+                "depth_func", "stencil_test", "stencil_func", "stencil_zpass", "stencil_zfail", "stencil_fail",
+                "stencil_ref", "stencil_mask", "stencil_writemask", "texture_enabled", "texture_envmode",
+                "texture_minfilter", "texture_magfilter", "texture_addressU", "texture_addressV", "blend_enabled",
+                "blend_src", "blend_dst"]
+FORMAT_BPP = {1: 1, 2: 1, 3: 2, 4: 2, 5: 4, 6: 2, 8: 2}  # cocogfx ePixelFormat -> bytes per texel
+
+
+def _walk(blob):
+    """-> ([(texture header offset, format, width, height, size)], [offset of each draw's 24 state words])"""
+    import struct
+    nd, nt = struct.unpack_from("<II", blob, 8)
+    p, texs, draws = 16, [], []
+    for _ in range(nt):
+        tid, fmt, w, h, sz = struct.unpack_from("<5I", blob, p)
+        texs.append((p, fmt, w, h, sz))
+        p += 20 + ((sz + 3) & ~3)
+    for _ in range(nd):
+        draws.append(p)
+        nv, npr = struct.unpack_from("<II", blob, p + 112 + 4 + 24)
+        p += 112 + 4 + 24 + 8 + nv * 40 + npr * 12
+    return texs, draws
+
+
+def mutate(blob, texture_format=None, only_draws=None, **states):
+    """A copy of the trace with the given state fields overwritten in every draw (or `only_draws`), and
+    optionally every texture re-labelled as `texture_format` (skipped where the texels would not fit)."""
+    import struct
+    out = bytearray(blob)
+    texs, draws = _walk(blob)
+    for i, off in enumerate(draws):
+        if only_draws is not None and i not in only_draws:
+            continue
+        for k, v in states.items():
+            struct.pack_into("<I", out, off + 4 * STATE_FIELDS.index(k), v)
+    if texture_format is not None:
+        for off, fmt, w, h, sz in texs:
+            if w * h * FORMAT_BPP[texture_format] <= sz:
+                struct.pack_into("<I", out, off + 4, texture_format)
+    return bytes(out)
+
+
+def state_variants():
+    """(label, kwargs for mutate) -- every value the app can program into the OM / TEX units."""
+    v = []
+    for f in range(8):
+        v.append((f"depth_func={f}", dict(depth_test=1, depth_writemask=1, depth_func=f)))
+    v.append(("depth_nowrite", dict(depth_test=1, depth_writemask=0, depth_func=1)))
+    for s in range(11):
+        v.append((f"blend_src={s}", dict(blend_enabled=1, blend_src=s, blend_dst=5)))
+    for d in range(11):
+        v.append((f"blend_dst={d}", dict(blend_enabled=1, blend_src=4, blend_dst=d)))
+    for func, zpass, zfail, fail, ref, mask, wm in [(7, 1, 0, 0, 0x5a, 0xff, 0xff), (1, 2, 3, 4, 0x80, 0xf0, 0x0f),
+                                                    (5, 5, 1, 2, 0xff, 0xff, 0xff), (2, 3, 3, 3, 0xff, 0xff, 0xf0),
+                                                    (0, 4, 5, 1, 7, 0x3c, 0xff), (3, 2, 2, 5, 1, 0xff, 0xaa)]:
+        v.append((f"stencil={func},{zpass},{zfail},{fail}", dict(stencil_test=1, stencil_func=func, stencil_zpass=zpass,
+                                                               stencil_zfail=zfail, stencil_fail=fail, stencil_ref=ref,
+                                                               stencil_mask=mask, stencil_writemask=wm)))
+    for fmt in (1, 2, 3, 4, 5, 6, 8):
+        for mag in (1, 2):
+            for addr in (0, 1):
+                v.append((f"tex fmt={fmt} mag={mag} addr={addr}",
+                          dict(texture_format=fmt, texture_magfilter=mag, texture_addressU=addr)))
+    for wm in (0x0, 0x5, 0xA, 0x7):
+        v.append((f"color_writemask={wm:#x}", dict(color_writemask=wm)))
+    for ce, env in [(1, 3), (1, 2), (0, 3), (0, 2)]:
+        v.append((f"color_enabled={ce} envmode={env}", dict(color_enabled=ce, texture_envmode=env)))
+    v.append(("no texture", dict(texture_enabled=0, color_enabled=1)))
+    return v

@@ -143,3 +143,28 @@ def test_draw3d_app_compares_against_reference_golden(native, tmp_path):
     assert "PASSED!" in p.stdout
     got = np.asarray(Image.open(out_png).convert("RGBA"))
     assert np.array_equal(got, rgba)
+
+
+VARIANTS = od.state_variants()
+
+
+@pytest.mark.parametrize("label,kw", VARIANTS, ids=[v[0] for v in VARIANTS])
+def test_state_space_matches_oracle(d3, label, kw):
+    """Every depth function, blend factor, stencil function/op, texture format x filter x address mode,
+    colour write mask and texture-environment switch the app can program (generic kernel paths)."""
+    for name, w, h in (("vase", 160, 128), ("evilskull", 100, 100)):
+        blob = od.mutate(od.trace_blob(name), **kw)
+        with d3.Draw3D(w, h, flags=ALL_SW) as app:
+            fb, zb = app.frame(d3.Trace(blob=blob), depth=True)
+        fo, zo, _ = od.render(checker(), blob, w, h, threads=4)
+        assert int((fb != fo).sum()) == 0 and int((zb != zo).sum()) == 0, (label, name)
+
+
+def test_specialised_kernels_equal_the_generic_kernel(d3):
+    t = d3.Trace(blob=od.trace_blob("mouse"))
+    frames = []
+    for generic in (0, 1):
+        with d3.Draw3D(512, 512, flags=ALL_SW) as app:
+            app.dev.dcr_write(0x805, generic)  # VX_DCR_RASTER_EXT_GENERIC
+            frames.append(app.frame(t, depth=True))
+    assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])

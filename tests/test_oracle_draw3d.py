@@ -148,3 +148,21 @@ def test_draw3d_libraries_export_their_api(native):
                 "srt_draw3d_depth_buffer"):
         assert hasattr(app, sym), sym
     assert os.path.exists(os.path.join(os.path.dirname(native["vortex"]), "..", "bin", "draw3d"))
+
+
+VARIANTS = od.state_variants()
+
+
+@pytest.mark.parametrize("label,kw", VARIANTS, ids=[v[0] for v in VARIANTS])
+def test_oracle_state_space_matches_compiled_reference(label, kw):
+    """The traces only use a corner of the fixed-function state (LESS/LEQUAL depth, SRC_ALPHA blending, three
+    texture formats, bilinear + repeat).  Every other value the app can program is exercised by overwriting the
+    state words of a trace; the restatement must agree with the reference's own code on each."""
+    ref = od.reference()
+    if ref is None:
+        pytest.skip("oracle/_ref/libref_draw3d.so not built (needs /root/reference)")
+    for name, size in (("vase", 96), ("evilskull", 80)):
+        blob = od.mutate(od.trace_blob(name), **kw)
+        fo, zo, _ = od.render(od.oracle(), blob, size, size, threads=2)
+        fr, zr, _ = od.render(ref, blob, size, size, threads=2)
+        assert np.array_equal(fo, fr) and np.array_equal(zo, zr), (label, name)
