@@ -107,6 +107,15 @@ def build(force=False, verbose=False):
     if force or _stale(exe, d3_src + headers + [vx_so, host_so]):
         _run([CC, "-O2", "-ffp-contract=off", "-Wall", "-Wextra", "-I", INC, "-o", exe] + d3_src + link +
              ["-Wl,-rpath,$ORIGIN/../lib"], verbose)
+    # 5. kernel images: what an unmodified reference app passes to vx_upload_kernel_file("kernel.vxbin").
+    #    16-byte .vxbin header (kernel/scripts/vxbin.py:54-75) + the 16-byte pipeline descriptor of skybox_rt.h
+    import struct
+    for name, pipeline in (("raytrace", 1), ("draw3d", 2)):
+        path = os.path.join(LIB, name + ".vxbin")
+        image = struct.pack("<QQQII", 0x80000000, 0x80000000 + 64, 0x5452584F42594B53, pipeline, 1)
+        if force or not os.path.exists(path) or open(path, "rb").read() != image:
+            with open(path, "wb") as f:
+                f.write(image)
     return {"vortex": vx_so, "host": host_so, "draw3d": d3_so}
 
 

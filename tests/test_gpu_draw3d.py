@@ -168,3 +168,44 @@ def test_specialised_kernels_equal_the_generic_kernel(d3):
             app.dev.dcr_write(0x805, generic)  # VX_DCR_RASTER_EXT_GENERIC
             frames.append(app.frame(t, depth=True))
     assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])
+
+
+def test_kernel_vxbin_file_runs_the_reference_flow(d3, native):
+    """An unmodified reference app calls vx_upload_kernel_file("kernel.vxbin"); lib/draw3d.vxbin is that file.
+    Drive one draw by hand through the raw vx_* calls, exactly as tests/regression/draw3d/main.cpp does."""
+    import ctypes as C
+
+    from skybox_rt_b200 import vortex as vx
+    L = vx.lib()
+    blob = od.trace_blob("triangle")
+    t = d3.Trace(blob=blob)
+    W = H = 64
+    n, tb, pb, _ = t.binning(0, W, H)
+    with vx.Device() as dev:
+        k = C.c_void_p()
+        path = os.path.join(os.path.dirname(native["vortex"]), "draw3d.vxbin").encode()
+        assert L.vx_upload_kernel_file(dev.handle, path, C.byref(k)) == 0
+        kernel = vx.Buffer(dev, k, 32)
+        cbuf, zbuf = dev.alloc(W * H * 4), dev.alloc(W * H * 4)
+        cbuf.write(np.full(W * H, 0xFF000000, np.uint32))
+        zbuf.write(np.full(W * H, 0xFFFFFFFF, np.uint32))
+        tile, prim = dev.alloc(len(tb), vx.VX_MEM_READ), dev.alloc(len(pb), vx.VX_MEM_READ)
+        tile.write(tb)
+        prim.write(pb)
+        arg = np.zeros(288 // 4, np.uint32)  # kernel_arg_t of draw3d/common.h, mirrors left at zero: hardware-unit path
+        arg[268 // 4] = 6                     # log_num_tasks
+        arg[272 // 4], arg[276 // 4] = prim.address & 0xFFFFFFFF, prim.address >> 32
+        arg8 = arg.view(np.uint8)
+        arg8[281] = 1                         # color_enabled
+        RAS, OM = 28, 34                      # VX_DCR_RASTER_STATE_BEGIN, VX_DCR_OM_STATE_BEGIN
+        for a, v in [(RAS + 0, (tile.address // 64) & 0xFFFFFFFF), (RAS + 1, n), (RAS + 2, (prim.address // 64) & 0xFFFFFFFF),
+                     (RAS + 3, 120), (RAS + 4, W << 16), (RAS + 5, H << 16), (OM + 0, (cbuf.address // 64) & 0xFFFFFFFF),
+                     (OM + 1, W * 4), (OM + 2, 0xFFFFFFFF), (OM + 5, 0), (OM + 6, 0), (OM + 7, 0), (OM + 8, 0), (OM + 10, 0),
+                     (OM + 11, 0), (OM + 12, 0xFF), (OM + 13, 0), (OM + 14, 0), (OM + 15, (1 << 8) | 1)]:
+            dev.dcr_write(a, v)
+        args = dev.upload(arg)
+        dev.start(kernel, args)
+        dev.ready_wait()
+        fb = cbuf.read(np.empty((H, W), np.uint32))
+    gold = od.golden_framebuffer(os.path.join(od.GOLDEN_DIR, "triangle_ref_64.npy"))
+    assert np.array_equal(fb, gold)

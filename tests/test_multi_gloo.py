@@ -44,3 +44,44 @@ def test_strips_gathered_over_gloo_equal_single_rank_frame(tmp_path, world, w, h
     nodes, tris = o.bvh2_build(o.scene_cornell())
     full, _ = o.render(o.make_arg(w, h, 2, spp=2, seed=77), nodes, tris, threads=1)
     assert np.array_equal(np.load(out), full)
+
+
+def _raster_worker(rank, world, port, w, h, out_path):
+    """Raster path, N>1 host logic: the product's per-rank binning decides which tile rows a rank draws; the
+    oracle stands in for the GPU kernel (it renders the frame, the rank keeps only the rows its own tile
+    list covers); FrameGather with 32-row blocks puts the strips together on rank 0."""
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import _oracle_draw3d as od
+    from skybox_rt_b200 import draw3d as d3
+    from skybox_rt_b200.formats import rank_row_index
+    from skybox_rt_b200.multi import FrameGather
+    blob = od.trace_blob("vase")
+    t = d3.Trace(blob=blob)
+    full, _, _ = od.render(od.oracle(), blob, w, h, threads=1)
+    mine = np.full_like(full, 0xFF000000)  # cleared target
+    for d in range(t.num_drawcalls):
+        n, tb, _, _ = t.binning(d, w, h, fmt=d3.TILEBUF_WIDE, rank=rank, num_ranks=world)
+        hdr = np.frombuffer(tb[:n * 16], np.uint32).reshape(n, 4)
+        for ty in set(int(x >> 16) for x in hdr[:, 0]):
+            assert ty % world == rank
+            mine[ty * 32:(ty + 1) * 32] = full[ty * 32:(ty + 1) * 32]
+    rows = rank_row_index(h, 32, world, rank)
+    g = FrameGather(w, h, 32, torch.device("cpu"))
+    frame = g.gather(torch.from_numpy(mine.view(np.int32))[torch.from_numpy(rows)])
+    if rank == 0:
+        np.save(out_path, frame.numpy().view(np.uint32))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,w,h,port", [(2, 160, 128, 29541), (3, 96, 200, 29542)])
+def test_raster_tile_rows_gathered_over_gloo(tmp_path, native, world, w, h, port):
+    import _oracle_draw3d as od
+    out = str(tmp_path / "frame.npy")
+    mp.spawn(_raster_worker, args=(world, port, w, h, out), nprocs=world, join=True)
+    full, _, _ = od.render(od.oracle(), od.trace_blob("vase"), w, h, threads=1)
+    assert np.array_equal(np.load(out), full)
