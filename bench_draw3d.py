@@ -144,6 +144,7 @@ def native_arm(args, ClockSampler, load_peaks):
     caddr, zaddr = app.buffer_addresses()
     cbuf = torch.as_tensor(DevMem(caddr, W * H * 4), device="cuda").view(H, W)
     zbuf = torch.as_tensor(DevMem(zaddr, W * H * 4), device="cuda").view(H, W)
+    dev.dcr_write(0x806, args.ppt)  # VX_DCR_RASTER_EXT_PPT
     app.prepare(trace)
     prep = app.stats()
     draws = prep["draws_submitted"]

@@ -238,6 +238,7 @@ typedef struct {
 } srt_tile_header_wide_t; /* 16 B */
 #define VX_DCR_RASTER_EXT_TBUF_FORMAT 0x804 /* back-end DCR (outside the reference's ranges); 0 after open */
 #define VX_DCR_RASTER_EXT_GENERIC 0x805     /* 1 = never use the state-specialised kernels (A/B testing)   */
+#define VX_DCR_RASTER_EXT_PPT 0x806         /* pixels per thread: 0 = by grid size, 4 = quad, 1 = pixel    */
 
 typedef struct {
   uint8_t* tilebuf;   uint64_t tilebuf_size;

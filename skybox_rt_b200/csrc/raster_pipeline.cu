@@ -224,13 +224,19 @@ int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg) {
     P.counters = st->d_counters;
     st->counters_live = true;
   }
+  // one thread per pixel when the draw has too few tiles to fill the GPU with quad-per-thread CTAs
+  // (4 CTAs of 256 threads fit an SM); VX_DCR_RASTER_EXT_PPT forces 4 or 1 for A/B runs
+  uint32_t ppt = dev_dcr(dev, VX_DCR_RASTER_EXT_PPT);
+  if (ppt != 1 && ppt != 4) ppt = (P.num_tiles < 2u * (uint32_t)dev->prop.multiProcessorCount) ? 1 : 4;
+  if (stats) ppt = 4;  // the quad-test counter is defined per quad
   using kernel_t = void (*)(const RasterParams);
-#define SRT_ROW(S, T) {raster_tile_kernel<S, T, 0>, raster_tile_kernel<S, T, 1>, raster_tile_kernel<S, T, 2>}
-  static const kernel_t table[2][5][3] = {
-      {SRT_ROW(false, 0), SRT_ROW(false, 1), SRT_ROW(false, 2), SRT_ROW(false, 3), SRT_ROW(false, 4)},
-      {SRT_ROW(true, 0), SRT_ROW(true, 1), SRT_ROW(true, 2), SRT_ROW(true, 3), SRT_ROW(true, 4)}};
+#define SRT_ROW(S, T, N) {raster_tile_kernel<S, T, 0, N>, raster_tile_kernel<S, T, 1, N>, raster_tile_kernel<S, T, 2, N>}
+  static const kernel_t table[3][5][3] = {
+      {SRT_ROW(false, 0, 4), SRT_ROW(false, 1, 4), SRT_ROW(false, 2, 4), SRT_ROW(false, 3, 4), SRT_ROW(false, 4, 4)},
+      {SRT_ROW(true, 0, 4), SRT_ROW(true, 1, 4), SRT_ROW(true, 2, 4), SRT_ROW(true, 3, 4), SRT_ROW(true, 4, 4)},
+      {SRT_ROW(false, 0, 1), SRT_ROW(false, 1, 1), SRT_ROW(false, 2, 1), SRT_ROW(false, 3, 1), SRT_ROW(false, 4, 1)}};
 #undef SRT_ROW
-  table[stats ? 1 : 0][texk][blendk]<<<P.num_tiles, kRasterThreads, 0, dev->stream>>>(P);
+  table[stats ? 1 : (ppt == 1 ? 2 : 0)][texk][blendk]<<<P.num_tiles, ppt == 1 ? 1024 : kRasterThreads, 0, dev->stream>>>(P);
   VX_CUDA_OK(cudaGetLastError());
   dev->last_launches = 1;
   return 0;

@@ -314,8 +314,14 @@ __device__ __forceinline__ uint32_t mul_u8(int32_t fx, uint32_t k) { return (((u
 //   BLENDK 0 blending off | 1 any state | 2 SRC_A / ONE_MINUS_SRC_A, ADD (glBlendFunc(SRC_ALPHA, ONE_MINUS_SRC_ALPHA))
 // raster_pipeline.cu picks the instantiation from the decoded state; results are identical by construction
 // (same functions, constant arguments).
-template <bool STATS, int TEXK, int BLENDK>
-__global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const RasterParams P) {
+//
+// PPT = pixels per thread.  4: one thread per 2x2 quad, 256 threads per tile (best throughput: the coverage
+// tests are shared by four pixels).  1: one thread per pixel, 1024 threads per tile, for draws with fewer tiles
+// than the GPU has room for -- a tile's primitive list is a serial chain, and with 32 warps instead of 8
+// walking it the chain of the heaviest tile (the draw's critical path) is ~4x shorter.
+template <bool STATS, int TEXK, int BLENDK, int PPT>
+__global__ void __launch_bounds__(PPT == 4 ? kRasterThreads : 1024) raster_tile_kernel(const RasterParams P) {
+  constexpr uint32_t NT = PPT == 4 ? kRasterThreads : 1024;
   const uint32_t tex_fmt = TEXK == 2 ? VX_TEX_FORMAT_A8R8G8B8 : TEXK == 3 ? VX_TEX_FORMAT_R5G6B5 : TEXK == 4 ? VX_TEX_FORMAT_A8L8 : P.tex_format;
   const uint32_t tex_filter = TEXK >= 2 ? VX_TEX_FILTER_BILINEAR : P.tex_filter;
   const uint32_t tex_wrapu = TEXK >= 2 ? VX_TEX_WRAP_REPEAT : P.tex_wrapu, tex_wrapv = TEXK >= 2 ? VX_TEX_WRAP_REPEAT : P.tex_wrapv;
@@ -347,13 +353,15 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
     pids = reinterpret_cast<const uint32_t*>(h + 1) + (hv.y & 0xffff);
   }
   const uint32_t X0 = tile_x << RASTER_TILE_LOGSIZE, Y0 = tile_y << RASTER_TILE_LOGSIZE;
-  const uint32_t lx = ((warp & 1) << 4) + ((lane & 7) << 1), ly = ((warp >> 1) << 3) + ((lane >> 3) << 1);
-  const uint32_t px = X0 + lx, py = Y0 + ly;  // top-left pixel of this thread's quad
+  // PPT 4: warp = 16x8 pixels (8x4 quads); PPT 1: warp = 8x4 pixels.  Either way inside one 16x16 block.
+  const uint32_t lx = PPT == 4 ? ((warp & 1) << 4) + ((lane & 7) << 1) : ((warp & 3) << 3) + (lane & 7);
+  const uint32_t ly = PPT == 4 ? ((warp >> 1) << 3) + ((lane >> 3) << 1) : ((warp >> 2) << 2) + (lane >> 3);
+  const uint32_t px = X0 + lx, py = Y0 + ly;  // this thread's pixel / the top-left pixel of its quad
 
   // scissor per pixel (graphics.cpp:817-818); the app sets it to the render target
   uint32_t inside = 0;
 #pragma unroll
-  for (int p = 0; p < 4; ++p) {
+  for (int p = 0; p < PPT; ++p) {
     const uint32_t x = px + (p & 1), y = py + (p >> 1);
     if (x >= P.scissor_left && x < P.scissor_right && y >= P.scissor_top && y < P.scissor_bottom) inside |= 1u << p;
   }
@@ -364,7 +372,7 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
   const bool need_ds = P.om_depth_enabled || P.om_stencil_enabled;
   const bool need_col = P.color_write && (P.color_read || blend_enabled);
 #pragma unroll
-  for (int p = 0; p < 4; ++p) {
+  for (int p = 0; p < PPT; ++p) {
     if (inside & (1u << p)) {
       const size_t x = px + (p & 1), y = py + (p >> 1);
       if (need_ds) ds[p] = *reinterpret_cast<const uint32_t*>(P.zbuf + y * P.zbuf_pitch + x * 4);
@@ -377,7 +385,7 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
   for (uint32_t base = 0; base < pids_count; base += kPrimChunk) {
     const uint32_t n = min((uint32_t)kPrimChunk, pids_count - base);
     __syncthreads();  // previous chunk fully consumed
-    for (uint32_t w = tid; w < n * 30; w += kRasterThreads) {
+    for (uint32_t w = tid; w < n * 30; w += NT) {
       const uint32_t k = w / 30, j = w - k * 30;
       const uint32_t pid = __ldg(pids + base + k);
       s_prims[k][j] = __ldg(reinterpret_cast<const int32_t*>(P.primbuf + (size_t)pid * P.prim_stride) + j);
@@ -420,7 +428,7 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
       uint32_t mask = 0;
       int32_t bc[4][3];
 #pragma unroll
-      for (int p = 0; p < 4; ++p) {
+      for (int p = 0; p < PPT; ++p) {
         uint32_t neg = 0;
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
@@ -433,7 +441,7 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
       if (!mask) continue;
 
 #pragma unroll
-      for (int p = 0; p < 4; ++p) {
+      for (int p = 0; p < PPT; ++p) {
         if (!(mask & (1u << p))) continue;
         if (STATS) ++n_frag;
         // GRADIENTS_SW (kernel.cpp:37-44)
@@ -478,7 +486,7 @@ __global__ void __launch_bounds__(kRasterThreads) raster_tile_kernel(const Raste
 
   // write back what was touched
 #pragma unroll
-  for (int p = 0; p < 4; ++p) {
+  for (int p = 0; p < PPT; ++p) {
     const size_t x = px + (p & 1), y = py + (p >> 1);
     if (ds_dirty & (1u << p)) *reinterpret_cast<uint32_t*>(P.zbuf + y * P.zbuf_pitch + x * 4) = ds[p];
     if (col_dirty & (1u << p)) *reinterpret_cast<uint32_t*>(P.cbuf + y * P.cbuf_pitch + x * 4) = col[p];

@@ -209,3 +209,14 @@ def test_kernel_vxbin_file_runs_the_reference_flow(d3, native):
         fb = cbuf.read(np.empty((H, W), np.uint32))
     gold = od.golden_framebuffer(os.path.join(od.GOLDEN_DIR, "triangle_ref_64.npy"))
     assert np.array_equal(fb, gold)
+
+
+@pytest.mark.parametrize("name", ["mouse", "evilskull", "scene"])
+def test_pixel_per_thread_kernel_equals_quad_per_thread_kernel(d3, name):
+    t = d3.Trace(blob=od.trace_blob(name))
+    frames = []
+    for ppt in (4, 1):
+        with d3.Draw3D(700, 500, flags=ALL_SW) as app:
+            app.dev.dcr_write(0x806, ppt)  # VX_DCR_RASTER_EXT_PPT
+            frames.append(app.frame(t, depth=True))
+    assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])
