@@ -216,6 +216,9 @@ typedef struct {
 
 /* Loads a "SKBXTRC1" trace (tests/golden/make_raster_fixtures.py; plain or gzip'ed).  0 on success. */
 int srt_trace_load(const char* path, srt_trace_t* out);
+/* Loads one of the reference's own .cgltrace files (Boost XML archive of cocogfx::CGLTrace,
+ * third_party/cocogfx/src/cgltrace.cpp:24-165) without Boost.  Same result as the flat form. */
+int srt_trace_load_cgltrace(const char* path, srt_trace_t* out);
 /* Same from memory; the blob is copied. */
 int srt_trace_from_blob(const void* blob, uint64_t size, srt_trace_t* out);
 void srt_trace_free(srt_trace_t* trace);

@@ -79,6 +79,8 @@ int srt_trace_from_blob(const void* blob, uint64_t size, srt_trace_t* out) {
 
 int srt_trace_load(const char* path, srt_trace_t* out) {
   gzFile f;
+  size_t plen = path ? strlen(path) : 0;
+  if (plen > 9 && strcmp(path + plen - 9, ".cgltrace") == 0) return srt_trace_load_cgltrace(path, out);
   uint64_t cap = 1 << 20, n = 0;
   uint8_t* buf;
   int got, rc;

@@ -225,9 +225,9 @@ int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg) {
     st->counters_live = true;
   }
   // one thread per pixel when the draw has too few tiles to fill the GPU with quad-per-thread CTAs
-  // (4 CTAs of 256 threads fit an SM); VX_DCR_RASTER_EXT_PPT forces 4 or 1 for A/B runs
+  // (4 CTAs of 256 threads fit an SM: below 4 x #SM tiles the GPU is not full); VX_DCR_RASTER_EXT_PPT forces 4 or 1 for A/B runs
   uint32_t ppt = dev_dcr(dev, VX_DCR_RASTER_EXT_PPT);
-  if (ppt != 1 && ppt != 4) ppt = (P.num_tiles < 2u * (uint32_t)dev->prop.multiProcessorCount) ? 1 : 4;
+  if (ppt != 1 && ppt != 4) ppt = (P.num_tiles < 4u * (uint32_t)dev->prop.multiProcessorCount) ? 1 : 4;
   if (stats) ppt = 4;  // the quad-test counter is defined per quad
   using kernel_t = void (*)(const RasterParams);
 #define SRT_ROW(S, T, N) {raster_tile_kernel<S, T, 0, N>, raster_tile_kernel<S, T, 1, N>, raster_tile_kernel<S, T, 2, N>}

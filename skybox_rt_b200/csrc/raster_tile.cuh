@@ -87,12 +87,14 @@ __device__ __forceinline__ void unpack8888(uint32_t format, uint32_t texel, uint
       lo = texel & 0x00ff00ff;
       hi = (texel >> 8) & 0x00ff00ff;
       return;
-    case VX_TEX_FORMAT_R5G6B5:
-      r = ((texel >> 8) & 0xf8) | ((texel >> 13) & 0x07);
-      g = ((texel >> 3) & 0xfc) | ((texel >> 9) & 0x03);
-      b = ((texel << 3) & 0xf8) | ((texel >> 2) & 0x07);
-      a = 0xff;
-      break;
+    case VX_TEX_FORMAT_R5G6B5: {
+      // the reference widens by bit replication, c8 = (c5 << 3) | (c5 >> 2) and (c6 << 2) | (c6 >> 4)
+      // (graphics.cpp:84-89); that equals (c5 * 33) >> 2 and (c6 * 65) >> 4, done here on r and b at once
+      const uint32_t rb = ((texel & 0xf800u) << 5) | (texel & 0x1fu);  // r5 in the high half-word, b5 in the low
+      lo = ((rb * 33u) >> 2) & 0x00ff00ffu;
+      hi = 0x00ff0000u | ((((texel >> 5) & 0x3fu) * 65u) >> 4);
+      return;
+    }
     case VX_TEX_FORMAT_A1R5G5B5:
       r = ((texel >> 7) & 0xf8) | ((texel >> 12) & 0x07);
       g = ((texel >> 2) & 0xf8) | ((texel >> 7) & 0x07);

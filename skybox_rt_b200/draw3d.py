@@ -95,6 +95,12 @@ class Trace:
 
     def __init__(self, path=None, blob=None):
         self.s = TraceStruct()
+        if blob is None and str(path).endswith(".cgltrace"):  # the reference's Boost-XML archive, read in C
+            rc = host_lib().srt_trace_load(str(path).encode(), C.byref(self.s))
+            if rc != 0:
+                raise vx.VortexError(f"srt_trace_load({path}) failed with code {rc}")
+            self.blob = C.string_at(self.s.blob, self.s.blob_size)
+            return
         if blob is None:
             with (gzip.open(path, "rb") if str(path).endswith(".gz") else open(path, "rb")) as f:
                 blob = f.read()

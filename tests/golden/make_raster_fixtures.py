@@ -106,5 +106,14 @@ def main():
             np.save(os.path.join(OUT, fn[:-4] + ".npy"), png_to_argb(os.path.join(d3, fn)))
 
 
+def copy_raw_traces():
+    """Two of the reference's trace files verbatim (test DATA, 4 KB and 52 KB), so that the C reader of the
+    Boost-XML form (csrc/host/draw3d_cgltrace.c) is exercised where /root/reference does not exist."""
+    import shutil
+    for fn in ("triangle.cgltrace", "box.cgltrace"):
+        shutil.copyfile(os.path.join(REF, "tests/regression/draw3d", fn), os.path.join(OUT, fn))
+
+
 if __name__ == "__main__":
+    copy_raw_traces()
     main()
