@@ -137,8 +137,11 @@ def native_arm(args, ClockSampler, load_peaks):
     trace = d3.Trace(blob=blob)
     K, warm = args.steps, max(args.warmup, 3)
 
-    app = d3.Draw3D(W, H, flags=ALL_SW | d3.WIDE_TILES, rank=rank, num_ranks=world)
-    dev = app.dev
+    # The device outlives every torch tensor that touched its stream (NCCL records its buffers on the stream it ran
+    # on; freeing them after vx_dev_close destroyed that stream aborts at interpreter exit), so it is opened here and
+    # left to process teardown.
+    dev = vx.Device()
+    app = d3.Draw3D(W, H, flags=ALL_SW | d3.WIDE_TILES, rank=rank, num_ranks=world, device=dev)
     stream = torch.cuda.ExternalStream(dev.cuda_stream(), device=torch.device("cuda", local))
     flush = torch.empty((256 << 20) // 4, dtype=torch.int32, device="cuda")
     caddr, zaddr = app.buffer_addresses()
