@@ -173,6 +173,43 @@ typedef struct {
 #define VX_CSR_RT_LAUNCHES     0x7C7 /* kernels launched by the last vx_start                */
 
 /* ------------------------------------------------------------------------------------
+ * Performance monitor, reference numbering (hw/rtl/VX_types.vh:27, :35-40, :66-247).
+ * VX_DCR_BASE_MPM_CLASS selects what the class CSRs 0xB03.. mean; the reference's stub writes
+ * it from the VORTEX_PROFILING environment variable before every vx_start
+ * (runtime/stub/vortex.cpp:142-149) and so does this library.  While the class is non-zero
+ * the kernels run their counting instantiations and VX_CSR_MCYCLE / VX_CSR_MINSTRET / the
+ * class CSRs ACCUMULATE over every run since vx_dev_open (free-running, like the hardware);
+ * with class 0 they describe the last vx_start.  core_id = SM index: MINSTRET is the work
+ * (rays, fragments) started on that SM, MCYCLE is the same for every SM, and the TEX / RASTER
+ * / OM / MEM class counters are device totals reported by every core -- the reference sums
+ * them over cores and divides by the core count (runtime/stub/utils.cpp:726-729, :747-750).
+ * Latency, stall and cache-miss CSRs of a class read 0: nothing inside a CUDA kernel measures
+ * them (ncu does; profiles/).
+ * ---------------------------------------------------------------------------------- */
+#define VX_DCR_BASE_MPM_CLASS   0x005
+#define VX_DCR_MPM_CLASS_NONE   0
+#define VX_DCR_MPM_CLASS_CORE   1
+#define VX_DCR_MPM_CLASS_MEM    2
+#define VX_DCR_MPM_CLASS_TEX    3
+#define VX_DCR_MPM_CLASS_RASTER 4
+#define VX_DCR_MPM_CLASS_OM     5
+#define VX_CSR_MPM_USER         0xB03 /* first class-dependent CSR */
+#define VX_CSR_MPM_USER_END     0xB20
+#define VX_CSR_MPM_LOADS        0xB0D /* CORE: records read  (nodes + triangles | tile, primitive, texel, framebuffer) */
+#define VX_CSR_MPM_STORES       0xB0E /* CORE: words written (pixels | framebuffer words)                             */
+#define VX_CSR_MPM_MEM_READS    0xB18 /* MEM: same as LOADS  */
+#define VX_CSR_MPM_MEM_WRITES   0xB19 /* MEM: same as STORES */
+#define VX_CSR_MPM_MEM_LT       0xB1A
+#define VX_CSR_MPM_TEX_READS    0xB03 /* TEX: texels fetched */
+#define VX_CSR_MPM_TCACHE_READS 0xB06
+#define VX_CSR_MPM_RASTER_READS 0xB03 /* RASTER: tile headers + primitive ids + primitive records read */
+#define VX_CSR_MPM_RCACHE_READS 0xB06
+#define VX_CSR_MPM_OM_READS     0xB03 /* OM: framebuffer words (colour, depth/stencil) read    */
+#define VX_CSR_MPM_OM_WRITES    0xB04 /* OM: framebuffer words written                          */
+#define VX_CSR_MPM_OCACHE_READS 0xB07
+#define VX_CSR_MPM_OCACHE_WRITES 0xB08
+
+/* ------------------------------------------------------------------------------------
  * Host builder (libskybox_rt_host: plain C, no CUDA) -- the pre-pass that plays the role
  * of graphics::Binning for this path.  Deterministic: same soup => same bytes.
  * ---------------------------------------------------------------------------------- */

@@ -103,7 +103,7 @@ int main(int argc, char* argv[]) {
            (unsigned long long)st->prims);
     printf("Total elapsed time: %lg ms (binning %lg, upload %lg, run %lg)\n", st->bin_ms + st->upload_ms + st->run_ms,
            st->bin_ms, st->upload_ms, st->run_ms);
-    vx_dump_perf(device, stdout);
+    if (!getenv("VORTEX_PROFILING")) vx_dump_perf(device, stdout); /* with it set, vx_dev_close dumps */
   }
   if (rc == 0 && strcmp(output_file, "null") != 0) {
     uint32_t* pixels = (uint32_t*)malloc((size_t)dst_width * dst_height * 4);

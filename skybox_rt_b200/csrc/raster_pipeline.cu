@@ -22,8 +22,12 @@
 
 namespace srt {
 
+// counter slots written by the STATS instantiations of raster_tile_kernel
+enum { RCTR_FRAGMENTS = 0, RCTR_TESTS, RCTR_TEXELS, RCTR_OM_READS, RCTR_OM_WRITES, RCTR_RASTER_READS, RCTR_PER_SM = 8,
+       RCTR_COUNT = 8 + kMaxSms };
+
 struct RasterState {
-  unsigned long long* d_counters = nullptr;  // [0] fragments, [1] quad-primitive tests
+  unsigned long long* d_counters = nullptr;  // RCTR_COUNT u64
   bool counters_live = false;                // the last launch counted
 };
 
@@ -217,10 +221,10 @@ int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg) {
     texk = texk ? 1 : 0;
     blendk = blendk ? 1 : 0;
   }
-  const bool stats = dev_dcr(dev, VX_DCR_RT_STATS) != 0;
+  const bool stats = vx_dev_counting(dev);
   if (stats) {
-    if (!st->d_counters) VX_CUDA_OK(cudaMalloc(&st->d_counters, 2 * sizeof(unsigned long long)));
-    VX_CUDA_OK(cudaMemsetAsync(st->d_counters, 0, 2 * sizeof(unsigned long long), dev->stream));
+    if (!st->d_counters) VX_CUDA_OK(cudaMalloc(&st->d_counters, RCTR_COUNT * sizeof(unsigned long long)));
+    VX_CUDA_OK(cudaMemsetAsync(st->d_counters, 0, RCTR_COUNT * sizeof(unsigned long long), dev->stream));
     P.counters = st->d_counters;
     st->counters_live = true;
   }
@@ -245,12 +249,19 @@ int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg) {
 int raster_read_counters(vx_device* dev) {
   RasterState* st = dev->raster;
   dev->last_raster_fragments = dev->last_raster_tests = 0;
+  memset(dev->last_raster_cls, 0, sizeof(dev->last_raster_cls));
+  memset(dev->last_instrs_sm, 0, sizeof(dev->last_instrs_sm));
   if (!st || !st->counters_live) return 0;
-  unsigned long long c[2] = {0, 0};
+  unsigned long long c[RCTR_COUNT];
   VX_CUDA_OK(cudaMemcpyAsync(c, st->d_counters, sizeof(c), cudaMemcpyDeviceToHost, dev->stream));
   VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
-  dev->last_raster_fragments = c[0];
-  dev->last_raster_tests = c[1];
+  dev->last_raster_fragments = c[RCTR_FRAGMENTS];
+  dev->last_raster_tests = c[RCTR_TESTS];
+  dev->last_raster_cls[0] = c[RCTR_TEXELS];
+  dev->last_raster_cls[1] = c[RCTR_OM_READS];
+  dev->last_raster_cls[2] = c[RCTR_OM_WRITES];
+  dev->last_raster_cls[3] = c[RCTR_RASTER_READS];
+  for (int i = 0; i < kMaxSms; ++i) dev->last_instrs_sm[i] = c[RCTR_PER_SM + i];
   return 0;
 }
 

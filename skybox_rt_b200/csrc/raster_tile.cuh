@@ -52,7 +52,7 @@ struct RasterParams {
   // switches
   uint8_t depth_writemask, color_read, color_write, om_depth_enabled, om_stencil_enabled, blend_enabled;
   uint8_t sh_depth, sh_color, sh_tex, sh_modulate;  // kernel_arg_t booleans
-  unsigned long long* counters;                      // [0] fragments shaded, [1] (quad, primitive) pairs tested
+  unsigned long long* counters;                      // RCTR_* slots of raster_pipeline.cu (STATS instantiations only)
 };
 
 constexpr int kRasterThreads = 256;
@@ -383,6 +383,8 @@ __global__ void __launch_bounds__(PPT == 4 ? kRasterThreads : 1024) raster_tile_
   }
 
   unsigned long long n_frag = 0, n_tested = 0;
+  uint32_t n_om_rd = 0;
+  if (STATS) n_om_rd = (uint32_t)__popc(inside) * ((need_ds ? 1u : 0u) + (need_col ? 1u : 0u));
 
   for (uint32_t base = 0; base < pids_count; base += kPrimChunk) {
     const uint32_t n = min((uint32_t)kPrimChunk, pids_count - base);
@@ -494,15 +496,25 @@ __global__ void __launch_bounds__(PPT == 4 ? kRasterThreads : 1024) raster_tile_
     if (col_dirty & (1u << p)) *reinterpret_cast<uint32_t*>(P.cbuf + y * P.cbuf_pitch + x * 4) = col[p];
   }
 
-  if (STATS) {
+  if (STATS) {  // slots: raster_pipeline.cu RCTR_*
+    uint32_t n_om_wr = (uint32_t)(__popc(ds_dirty) + __popc(col_dirty));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       n_frag += __shfl_xor_sync(0xffffffffu, n_frag, o);
       n_tested += __shfl_xor_sync(0xffffffffu, n_tested, o);
+      n_om_rd += __shfl_xor_sync(0xffffffffu, n_om_rd, o);
+      n_om_wr += __shfl_xor_sync(0xffffffffu, n_om_wr, o);
     }
     if (lane == 0) {
+      uint32_t smid;
+      asm("mov.u32 %0, %%smid;" : "=r"(smid));
       atomicAdd(P.counters + 0, n_frag);
       atomicAdd(P.counters + 1, n_tested);
+      if (sh_tex) atomicAdd(P.counters + 2, n_frag * (tex_filter ? 4ull : 1ull));  // texels fetched
+      atomicAdd(P.counters + 3, (unsigned long long)n_om_rd);                       // framebuffer words read
+      atomicAdd(P.counters + 4, (unsigned long long)n_om_wr);                       // framebuffer words written
+      if (warp == 0) atomicAdd(P.counters + 5, 1ull + 2ull * pids_count);           // tile header + pid + primitive records
+      atomicAdd(P.counters + 8 + (smid & 255u), n_frag);                            // fragments per SM
     }
   }
 }

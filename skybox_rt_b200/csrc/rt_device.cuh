@@ -183,17 +183,22 @@ __device__ __forceinline__ V3 bounce_dir(uint32_t seed_hash, uint32_t pix, uint3
 
 struct Stats {
   uint32_t nodes, tris;  // node records fetched / triangles tested by this thread
+  uint32_t rays;         // rays started by this thread
 };
 
 // Per-thread traversal statistics -> device counters (warp reduce, one atomic per warp).  All 32
-// lanes of the warp must call this.  Counter slots: vx_internal.h CTR_NODES = 2, CTR_TRIS = 3.
+// lanes of the warp must call this.  Counter slots: vx_internal.h CTR_NODES = 2, CTR_TRIS = 3, CTR_PER_SM = 8.
 template <class S>
 __device__ __forceinline__ void flush_stats(const S& st, unsigned long long* counters) {
   const uint32_t n = __reduce_add_sync(0xffffffffu, st.nodes);
   const uint32_t t = __reduce_add_sync(0xffffffffu, st.tris);
+  const uint32_t r = __reduce_add_sync(0xffffffffu, st.rays);
   if ((threadIdx.x & 31) == 0) {
     if (n) atomicAdd(counters + 2, (unsigned long long)n);
     if (t) atomicAdd(counters + 3, (unsigned long long)t);
+    uint32_t smid;
+    asm("mov.u32 %0, %%smid;" : "=r"(smid));
+    if (r) atomicAdd(counters + 8 + (smid & 255u), (unsigned long long)r);
   }
 }
 

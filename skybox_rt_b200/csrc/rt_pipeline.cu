@@ -178,7 +178,7 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   }
   if (rt_state(dev, &st) != 0) return -1;
   cudaStream_t s = dev->stream;
-  const bool stats = dev->dcrs.count(VX_DCR_RT_STATS) && dev->dcrs[VX_DCR_RT_STATS] != 0;
+  const bool stats = vx_dev_counting(dev);
   const uint32_t variant = dev->dcrs.count(VX_DCR_RT_VARIANT) ? dev->dcrs[VX_DCR_RT_VARIANT] : 0u;
   if (variant > 3u) {
     fprintf(stderr, "[VXDRV] raytrace: unknown kernel variant %u\n", variant);
@@ -243,6 +243,7 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
 
   if (a.mode == SRT_MODE_RAYS) {
     dev->last_rays_primary = a.num_rays;
+    dev->last_rt_stores = a.num_rays;
     // the job cursor is 32 bits wide: long lists go out in slices of 2^30 rays
     const uint64_t slice = 1ull << 30;
     for (uint64_t first = 0; first < a.num_rays; first += slice) {
@@ -283,6 +284,7 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
 
   const uint32_t rows = srt_rank_rows(a.dst_height, a.rows_per_block, a.num_ranks, a.rank_id);
   dev->last_rays_primary = (uint64_t)rows * a.dst_width * a.spp;
+  dev->last_rt_stores = (uint64_t)rows * a.dst_width;
   if (rows == 0) return 0;
   const uint32_t tiles = ((a.dst_width + 7) / 8) * ((rows + 3) / 4);  // one 8x4 pixel tile = 32 jobs
   if (wide) {
@@ -306,6 +308,7 @@ int rt_read_counters(vx_device* dev) {
   unsigned long long h[CTR_COUNT];
   VX_CUDA_OK(cudaMemcpy(h, dev->rt->d_counters, sizeof(h), cudaMemcpyDeviceToHost));
   for (int i = 0; i < CTR_COUNT; ++i) dev->last_counters[i] = h[i];
+  for (int i = 0; i < kMaxSms; ++i) dev->last_instrs_sm[i] = h[CTR_PER_SM + i];
   dev->last_counters_valid = true;
   return 0;
 }

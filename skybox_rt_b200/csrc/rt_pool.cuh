@@ -249,7 +249,7 @@ rt_pool_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
   const uint32_t warp_in_cta = threadIdx.x >> 5;
   const size_t warp_gid = (size_t)blockIdx.x * (kPoolThreads / 32) + warp_in_cta;
   PoolCtx c = {pools + warp_in_cta, spill + warp_gid * (size_t)(kPoolSlots * kPoolSpill)};
-  Stats stats = {0u, 0u};
+  Stats stats = {0u, 0u, 0u};
   WarpPool& wp = *c.wp;
   auto collect = [&](uint32_t slot) {
     const uint32_t rec = wp.f[F_BEST_REC][slot];
@@ -267,6 +267,7 @@ rt_pool_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
   };
   auto spawn = [&](uint32_t slot, uint32_t job) -> bool {
     const float4 r0 = __ldg(rays + 2 * (size_t)job), r1 = __ldg(rays + 2 * (size_t)job + 1);
+    if (STATS) stats.rays += 1;
     pool_put_ray(wp, slot, mk(r0.x, r0.y, r0.z), mk(r1.x, r1.y, r1.z), r0.w, r1.w, false, job);
     return true;
   };

@@ -310,7 +310,7 @@ rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc
   PathState ps = {};
   RayState r;
   Hit best;
-  Stats stats = {0u, 0u};
+  Stats stats = {0u, 0u, 0u};
   Cursor cu;
   uint32_t n_shadow = 0u, n_bounce = 0u;
   bool have_job = false;
@@ -319,6 +319,7 @@ rt_wide_render_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc
   ray_setup(r, cam.eye, cam.fwd, 0.0f, false);
 
   auto start_ray = [&](V3 o, V3 d, float tmax, bool any) {
+    if (STATS) stats.rays += 1;
     ray_setup(r, o, d, 0.0f, any);
     best.t = tmax; best.prim = SRT_MISS; best.rec = 0u;
     st.sp = 0;
@@ -440,7 +441,7 @@ rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
   Pool pool = {0u, 0u, false};
   RayState r;
   Hit best;
-  Stats stats = {0u, 0u};
+  Stats stats = {0u, 0u, 0u};
   Cursor cu;
   uint32_t my_ray = 0u;
   bool have_job = false;
@@ -458,6 +459,7 @@ rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
       const float4 r0 = __ldg(rays + 2 * (size_t)job), r1 = __ldg(rays + 2 * (size_t)job + 1);
       my_ray = job;
       have_job = true;
+      if (STATS) stats.rays += 1;
       ray_setup(r, mk(r0.x, r0.y, r0.z), mk(r1.x, r1.y, r1.z), r0.w, false);
       best.t = r1.w; best.u = 0.0f; best.v = 0.0f; best.prim = SRT_MISS; best.rec = 0u;
       st.sp = 0;

@@ -105,7 +105,14 @@ int vx_dev_open(vx_device_h* hdevice) {
   dev->last_pipeline = 0;
   dev->last_launches = 0;
   dev->last_node_bytes = 0;
+  dev->last_rt_stores = 0;
   memset(dev->last_counters, 0, sizeof(dev->last_counters));
+  memset(dev->last_raster_cls, 0, sizeof(dev->last_raster_cls));
+  memset(dev->last_instrs_sm, 0, sizeof(dev->last_instrs_sm));
+  memset(dev->acc, 0, sizeof(dev->acc));
+  memset(dev->acc_instrs_sm, 0, sizeof(dev->acc_instrs_sm));
+  dev->harvested = true;
+  dev->run_mpm_class = 0;
   if (cudaSetDevice(ordinal) != cudaSuccess || cudaGetDeviceProperties(&dev->prop, ordinal) != cudaSuccess ||
       cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&dev->ev_start) != cudaSuccess || cudaEventCreate(&dev->ev_stop) != cudaSuccess) {
@@ -230,6 +237,52 @@ int vx_copy_from_dev(void* host_ptr, vx_buffer_h hbuffer, uint64_t src_offset, u
 }
 
 // ------------------------------------------------------------------------------- execution
+namespace {
+
+// Wait for the last run, bring its device counters into dev->last_*, and -- if it ran with the performance
+// monitor on -- add them to the free-running accumulators.  Idempotent per run.
+int harvest(vx_device* dev) {
+  if (dev->harvested) return 0;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  dev->harvested = true;
+  float ms = 0.0f;
+  if (dev->run_recorded) VX_CUDA_OK(cudaEventElapsedTime(&ms, dev->ev_start, dev->ev_stop));
+  if (dev->last_pipeline == SRT_PIPELINE_RAYTRACE) {
+    if (srt::rt_read_counters(dev) != 0) return -1;
+  } else if (dev->last_pipeline == SRT_PIPELINE_DRAW3D) {
+    if (srt::raster_read_counters(dev) != 0) return -1;
+    dev->last_counters_valid = true;
+  }
+  if (dev->run_mpm_class == 0) return 0;
+  uint64_t* a = dev->acc;
+  a[VX_PERF_CYCLES] += (uint64_t)((double)ms * 1e-3 * (double)dev->prop.clockRate * 1e3);
+  a[VX_PERF_NS] += (uint64_t)((double)ms * 1e6);
+  a[VX_PERF_RUNS] += 1;
+  if (dev->last_pipeline == SRT_PIPELINE_RAYTRACE) {
+    const uint64_t* c = dev->last_counters;
+    a[VX_PERF_RT_PRIMARY] += dev->last_rays_primary;
+    a[VX_PERF_RT_SHADOW] += c[CTR_RAYS_SHADOW];
+    a[VX_PERF_RT_BOUNCE] += c[CTR_RAYS_BOUNCE];
+    a[VX_PERF_RT_NODES] += c[CTR_NODES];
+    a[VX_PERF_RT_TRIS] += c[CTR_TRIS];
+    a[VX_PERF_RT_NODE_BYTES] += c[CTR_NODES] * dev->last_node_bytes;
+    a[VX_PERF_RT_STORES] += dev->last_rt_stores;
+  } else {
+    a[VX_PERF_FRAGMENTS] += dev->last_raster_fragments;
+    a[VX_PERF_TESTS] += dev->last_raster_tests;
+    a[VX_PERF_TILES] += dev->last_raster_tiles;
+    a[VX_PERF_TEX_READS] += dev->last_raster_cls[0];
+    a[VX_PERF_OM_READS] += dev->last_raster_cls[1];
+    a[VX_PERF_OM_WRITES] += dev->last_raster_cls[2];
+    a[VX_PERF_RASTER_READS] += dev->last_raster_cls[3];
+  }
+  for (int i = 0; i < kMaxSms; ++i) dev->acc_instrs_sm[i] += dev->last_instrs_sm[i];
+  return 0;
+}
+
+}  // namespace
+
 int vx_start(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments) {
   if (nullptr == hdevice || nullptr == hkernel || nullptr == harguments) return -1;
   vx_device* dev = as_dev(hdevice);
@@ -248,6 +301,13 @@ int vx_start(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments) {
     return -1;
   }
   VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  // VORTEX_PROFILING=<class> turns the performance monitor on for every run (stub/vortex.cpp:142-149)
+  static const int profiling_mode = env_int("VORTEX_PROFILING", 0);
+  if (profiling_mode != 0) dev->dcrs[VX_DCR_BASE_MPM_CLASS] = (uint32_t)profiling_mode;
+  // a profiled run that nobody read yet goes into the accumulators before its counters are reused
+  if (dev->run_mpm_class != 0 && harvest(dev) != 0) return -1;
+  dev->run_mpm_class = (int)vx_dev_dcr(dev, VX_DCR_BASE_MPM_CLASS);
+  dev->harvested = false;
   VX_CUDA_OK(cudaEventRecord(dev->ev_start, dev->stream));
   int rc = -1;
   dev->last_counters_valid = false;
@@ -332,42 +392,85 @@ int vx_dcr_read(vx_device_h hdevice, uint32_t addr, uint32_t* value) {
 int vx_mpm_query(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t* value) {
   if (nullptr == hdevice || nullptr == value) return -1;
   vx_device* dev = as_dev(hdevice);
-  (void)core_id;  // counters are device totals; every core id reports the total
-  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
-  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  if (core_id >= (uint32_t)dev->prop.multiProcessorCount) return -1;
+  if (harvest(dev) != 0) return -1;
   float ms = 0.0f;
   if (dev->run_recorded) VX_CUDA_OK(cudaEventElapsedTime(&ms, dev->ev_start, dev->ev_stop));
-  if (!dev->last_counters_valid && dev->last_pipeline == SRT_PIPELINE_RAYTRACE) srt::rt_read_counters(dev);
-  if (dev->last_pipeline == SRT_PIPELINE_DRAW3D) {
-    if (!dev->last_counters_valid) {
-      srt::raster_read_counters(dev);
-      dev->last_counters_valid = true;
+  const uint32_t cls = vx_dev_dcr(dev, VX_DCR_BASE_MPM_CLASS);
+  const bool draw3d = dev->last_pipeline == SRT_PIPELINE_DRAW3D;
+  const uint64_t* c = dev->last_counters;
+  const uint64_t* a = dev->acc;
+  const uint64_t last_instrs =
+      draw3d ? dev->last_raster_fragments : dev->last_rays_primary + c[CTR_RAYS_SHADOW] + c[CTR_RAYS_BOUNCE];
+  // the two CSRs every class has (include/skybox_rt.h: accumulated while the monitor is on, else the last run)
+  if (addr == VX_CSR_MCYCLE) {
+    *value = cls ? a[VX_PERF_CYCLES] : (uint64_t)((double)ms * 1e-3 * (double)dev->prop.clockRate * 1e3);
+    return 0;
+  }
+  if (addr == VX_CSR_MINSTRET) {
+    *value = cls ? dev->acc_instrs_sm[core_id] : (core_id == 0 ? last_instrs : 0);
+    return 0;
+  }
+  if (addr >= VX_CSR_MPM_USER && addr < VX_CSR_MPM_USER_END) {  // class CSRs
+    const uint64_t reads = a[VX_PERF_RT_NODES] + a[VX_PERF_RT_TRIS] + a[VX_PERF_RASTER_READS] + a[VX_PERF_TEX_READS] + a[VX_PERF_OM_READS];
+    const uint64_t writes = a[VX_PERF_RT_STORES] + a[VX_PERF_OM_WRITES];
+    uint64_t v = 0;
+    switch (cls) {
+      case VX_DCR_MPM_CLASS_CORE:
+        if (addr == VX_CSR_MPM_LOADS) v = reads;
+        else if (addr == VX_CSR_MPM_STORES) v = writes;
+        break;
+      case VX_DCR_MPM_CLASS_MEM:
+        if (addr == VX_CSR_MPM_MEM_READS) v = reads;
+        else if (addr == VX_CSR_MPM_MEM_WRITES) v = writes;
+        break;
+      case VX_DCR_MPM_CLASS_TEX:
+        if (addr == VX_CSR_MPM_TEX_READS || addr == VX_CSR_MPM_TCACHE_READS) v = a[VX_PERF_TEX_READS];
+        break;
+      case VX_DCR_MPM_CLASS_RASTER:
+        if (addr == VX_CSR_MPM_RASTER_READS || addr == VX_CSR_MPM_RCACHE_READS) v = a[VX_PERF_RASTER_READS];
+        break;
+      case VX_DCR_MPM_CLASS_OM:
+        if (addr == VX_CSR_MPM_OM_READS || addr == VX_CSR_MPM_OCACHE_READS) v = a[VX_PERF_OM_READS];
+        else if (addr == VX_CSR_MPM_OM_WRITES || addr == VX_CSR_MPM_OCACHE_WRITES) v = a[VX_PERF_OM_WRITES];
+        break;
+      default: break;
     }
+    *value = v;  // latency / stall / miss counters have no source inside a CUDA kernel: they read 0
+    return 0;
+  }
+  // back-end CSRs: totals of the last vx_start
+  switch (addr) {
+    case VX_CSR_RT_ELAPSED_NS: *value = (uint64_t)((double)ms * 1e6); return 0;
+    case VX_CSR_RT_LAUNCHES: *value = dev->last_launches; return 0;
+    default: break;
+  }
+  if (draw3d) {
     switch (addr) {
-      case VX_CSR_MCYCLE: *value = (uint64_t)((double)ms * 1e-3 * (double)dev->prop.clockRate * 1e3); return 0;
-      case VX_CSR_MINSTRET: *value = dev->last_raster_fragments; return 0;
       case VX_CSR_RASTER_FRAGMENTS: *value = dev->last_raster_fragments; return 0;
       case VX_CSR_RASTER_QUAD_TESTS: *value = dev->last_raster_tests; return 0;
       case VX_CSR_RASTER_TILES: *value = dev->last_raster_tiles; return 0;
-      case VX_CSR_RT_ELAPSED_NS: *value = (uint64_t)((double)ms * 1e6); return 0;
-      case VX_CSR_RT_LAUNCHES: *value = dev->last_launches; return 0;
       default: return -1;
     }
   }
-  const uint64_t* c = dev->last_counters;
   switch (addr) {
-    case VX_CSR_MCYCLE: *value = (uint64_t)((double)ms * 1e-3 * (double)dev->prop.clockRate * 1e3); break;
-    case VX_CSR_MINSTRET: *value = dev->last_rays_primary + c[CTR_RAYS_SHADOW] + c[CTR_RAYS_BOUNCE]; break;
     case VX_CSR_RT_RAYS_PRIMARY: *value = dev->last_rays_primary; break;
     case VX_CSR_RT_RAYS_SHADOW: *value = c[CTR_RAYS_SHADOW]; break;
     case VX_CSR_RT_RAYS_BOUNCE: *value = c[CTR_RAYS_BOUNCE]; break;
     case VX_CSR_RT_NODES: *value = c[CTR_NODES]; break;
     case VX_CSR_RT_TRIS: *value = c[CTR_TRIS]; break;
-    case VX_CSR_RT_ELAPSED_NS: *value = (uint64_t)((double)ms * 1e6); break;
     case VX_CSR_RT_NODE_BYTES: *value = dev->last_node_bytes; break;
-    case VX_CSR_RT_LAUNCHES: *value = dev->last_launches; break;
     default: return -1;
   }
+  return 0;
+}
+
+// Accumulated totals of the performance monitor for vx_dump_perf (vx_utils.cpp); slots = VX_PERF_* of vx_internal.h.
+int vx_cuda_perf_totals(vx_device_h hdevice, uint64_t* out, uint32_t count) {
+  if (nullptr == hdevice || nullptr == out) return -1;
+  vx_device* dev = as_dev(hdevice);
+  if (harvest(dev) != 0) return -1;
+  for (uint32_t i = 0; i < count; ++i) out[i] = i < VX_PERF_COUNT ? dev->acc[i] : 0;
   return 0;
 }
 

@@ -14,6 +14,7 @@
 #include "skybox_draw3d.h"
 #include "skybox_rt.h"
 #include "vortex.h"
+#include "vortex_cuda.h"
 
 struct vx_device;
 
@@ -38,8 +39,13 @@ enum {
   CTR_NODES = 2,
   CTR_TRIS = 3,
   CTR_CURSOR = 4,  // job cursor of the persistent kernels
-  CTR_COUNT = 8
+  CTR_PER_SM = 8,  // rays started on each SM (%smid), STATS instantiations only
+  CTR_COUNT = 8 + 256
 };
+
+// Accumulators of the performance monitor: slots VX_PERF_* of include/vortex_cuda.h, free-running over every
+// profiled run since vx_dev_open, like the reference's MPM CSRs (hw/rtl/VX_types.vh:66-247).
+constexpr int kMaxSms = 256;
 
 namespace srt {
 struct RtState;      // rt_pipeline.cu
@@ -63,11 +69,19 @@ struct vx_device {
   int last_pipeline;
   uint32_t last_launches;       // kernels enqueued by the last vx_start
   uint32_t last_node_bytes;     // bytes per node fetch of the kernel variant that ran
+  uint64_t last_rt_stores;      // pixels (or hit records) written by the last run
   // raster pipeline (draw3d)
   srt::RasterState* raster;
   uint32_t last_raster_tiles;       // tiles (= CTAs) of the last draw
   uint64_t last_raster_fragments;   // fragments shaded    (only when VX_DCR_RT_STATS is on)
   uint64_t last_raster_tests;       // quad x primitive coverage tests (only when VX_DCR_RT_STATS is on)
+  uint64_t last_raster_cls[4];      // texels fetched, framebuffer words read, written, raster records read
+  // performance monitor
+  bool harvested;                   // the last run's counters are in last_* (and in acc when it ran profiled)
+  int run_mpm_class;                // VX_DCR_BASE_MPM_CLASS latched by the last vx_start
+  uint64_t last_instrs_sm[kMaxSms]; // work units (rays / fragments) per SM of the last run, counting runs only
+  uint64_t acc[VX_PERF_COUNT];
+  uint64_t acc_instrs_sm[kMaxSms];
 };
 
 // DCRs owned by this back-end (outside every range the reference decodes,
@@ -79,6 +93,15 @@ struct vx_device {
 #define VX_DCR_RT_KEEP_ACTIVE 0x802 /* tuning: refill threshold of the persistent kernels (1..32), 0 = default */
 #define VX_DCR_RT_PREFETCH 0x803 /* 1 = warm L2 with the scene before tracing when it fits (measured: no gain, off by default) */
 #define VX_DCR_RT_END     0x810
+
+inline uint32_t vx_dev_dcr(const vx_device* dev, uint32_t addr) {
+  auto it = dev->dcrs.find(addr);
+  return it == dev->dcrs.end() ? 0u : it->second;
+}
+// the counting instantiations run when asked for directly or when the performance monitor is on
+inline bool vx_dev_counting(const vx_device* dev) {
+  return vx_dev_dcr(dev, VX_DCR_RT_STATS) != 0 || vx_dev_dcr(dev, VX_DCR_BASE_MPM_CLASS) != 0;
+}
 
 namespace srt {
 // rt_pipeline.cu

@@ -14,6 +14,7 @@
 
 #include "skybox_rt.h"
 #include "vortex.h"
+#include "vortex_cuda.h"
 
 namespace {
 
@@ -109,23 +110,124 @@ int vx_check_occupancy(vx_device_h hdevice, uint32_t group_size, uint32_t* max_l
 
 // The reference prints one "PERF: instrs=, cycles=, IPC=" totals line that its CI greps
 // (stub/utils.cpp:800-803).  Here "instructions" are rays; the RT class lines follow.
+// Same shape as the reference's (runtime/stub/utils.cpp:159-805): the class comes from VORTEX_PROFILING
+// (:24-48), one pass over the cores reading MCYCLE / MINSTRET and the class CSRs, "PERF: core%d:" lines when
+// there is more than one core (:651-656), the class block with the reference's line formats (:658-797), then
+// the totals line every script greps (:799-800).  Between the two this back-end adds its own "PERF: rt:" /
+// "PERF: raster:" lines from vx_cuda_perf_totals.  CORE prints the two counters this back-end has a source
+// for (loads, stores); the pipeline-stall lines of the reference have no counterpart and are left out.
 int vx_dump_perf(vx_device_h hdevice, FILE* stream) {
   if (nullptr == hdevice || nullptr == stream) return -1;
-  uint64_t cycles = 0, rays = 0, prim = 0, shadow = 0, bounce = 0, nodes = 0, tris = 0, ns = 0;
-  vx_mpm_query(hdevice, VX_CSR_MCYCLE, 0, &cycles);
-  vx_mpm_query(hdevice, VX_CSR_MINSTRET, 0, &rays);
-  vx_mpm_query(hdevice, VX_CSR_RT_RAYS_PRIMARY, 0, &prim);
-  vx_mpm_query(hdevice, VX_CSR_RT_RAYS_SHADOW, 0, &shadow);
-  vx_mpm_query(hdevice, VX_CSR_RT_RAYS_BOUNCE, 0, &bounce);
-  vx_mpm_query(hdevice, VX_CSR_RT_NODES, 0, &nodes);
-  vx_mpm_query(hdevice, VX_CSR_RT_TRIS, 0, &tris);
-  vx_mpm_query(hdevice, VX_CSR_RT_ELAPSED_NS, 0, &ns);
-  const double ipc = cycles ? (double)rays / (double)cycles : 0.0;
-  fprintf(stream, "PERF: rt: rays_primary=%lu, rays_shadow=%lu, rays_bounce=%lu, nodes=%lu, tris=%lu, elapsed_ns=%lu\n",
-          (unsigned long)prim, (unsigned long)shadow, (unsigned long)bounce, (unsigned long)nodes,
-          (unsigned long)tris, (unsigned long)ns);
-  if (ns) fprintf(stream, "PERF: rt: Mrays/s=%f\n", (double)rays * 1e3 / (double)ns);
-  fprintf(stream, "PERF: instrs=%lu, cycles=%lu, IPC=%f\n", (unsigned long)rays, (unsigned long)cycles, ipc);
+  auto avg = [](uint64_t part, uint64_t total) -> double { return total ? (double)part / (double)total : 0.0; };
+  auto ratio = [](uint64_t part, uint64_t total) -> int {
+    return total ? (int)((1.0 - (double)part / (double)total) * 100) : 0;
+  };
+  auto percent = [&](uint64_t part, uint64_t total) -> int { return (int)(avg(part, total) * 100); };
+  static const int perf_class = getenv("VORTEX_PROFILING") ? atoi(getenv("VORTEX_PROFILING")) : 0;
+  uint64_t num_cores = 0;
+  int err = vx_dev_caps(hdevice, VX_CAPS_NUM_CORES, &num_cores);
+  if (err) return err;
+  // class CSRs, summed over the cores exactly as the reference does
+  uint64_t sum[VX_CSR_MPM_USER_END - VX_CSR_MPM_USER] = {0};
+  uint64_t total_instrs = 0, total_cycles = 0, max_cycles = 0;
+  for (unsigned core_id = 0; core_id < num_cores; ++core_id) {
+    uint64_t cycles_per_core = 0, instrs_per_core = 0, tmp = 0;
+    if ((err = vx_mpm_query(hdevice, VX_CSR_MCYCLE, core_id, &cycles_per_core)) != 0) return err;
+    if ((err = vx_mpm_query(hdevice, VX_CSR_MINSTRET, core_id, &instrs_per_core)) != 0) return err;
+    if (perf_class != VX_DCR_MPM_CLASS_NONE) {
+      for (uint32_t a = VX_CSR_MPM_USER; a < VX_CSR_MPM_USER_END; ++a) {
+        if ((err = vx_mpm_query(hdevice, a, core_id, &tmp)) != 0) return err;
+        sum[a - VX_CSR_MPM_USER] += tmp;
+      }
+    }
+    if (num_cores > 1 && (perf_class != VX_DCR_MPM_CLASS_NONE ? instrs_per_core != 0 : core_id == 0))
+      fprintf(stream, "PERF: core%d: instrs=%ld, cycles=%ld, IPC=%f\n", core_id, (long)instrs_per_core,
+              (long)cycles_per_core, (float)avg(instrs_per_core, cycles_per_core));
+    total_instrs += instrs_per_core;
+    total_cycles += cycles_per_core;
+    if (cycles_per_core > max_cycles) max_cycles = cycles_per_core;
+  }
+  auto csr = [&](uint32_t a) -> uint64_t { return num_cores ? sum[a - VX_CSR_MPM_USER] / num_cores : 0; };
+  switch (perf_class) {
+    case VX_DCR_MPM_CLASS_CORE:
+      fprintf(stream, "PERF: loads=%ld\n", (long)csr(VX_CSR_MPM_LOADS));
+      fprintf(stream, "PERF: stores=%ld\n", (long)csr(VX_CSR_MPM_STORES));
+      break;
+    case VX_DCR_MPM_CLASS_MEM: {
+      const uint64_t rd = csr(VX_CSR_MPM_MEM_READS), wr = csr(VX_CSR_MPM_MEM_WRITES);
+      fprintf(stream, "PERF: memory requests=%ld (reads=%ld, writes=%ld)\n", (long)(rd + wr), (long)rd, (long)wr);
+      fprintf(stream, "PERF: memory latency=%d cycles\n", (int)avg(csr(VX_CSR_MPM_MEM_LT), rd));
+    } break;
+    case VX_DCR_MPM_CLASS_TEX: {
+      const uint64_t rd = csr(0xB03), lat = csr(0xB04), stl = csr(0xB05);
+      fprintf(stream, "PERF: tex memory reads=%ld\n", (long)rd);
+      fprintf(stream, "PERF: tex memory latency=%d cycles\n", (int)avg(lat, rd));
+      fprintf(stream, "PERF: tex stalls=%ld (%d%%)\n", (long)stl, stl ? ratio(stl, total_cycles) : 0);
+      const uint64_t crd = csr(0xB06), cmiss = csr(0xB07), cbank = csr(0xB08), cmshr = csr(0xB09);
+      fprintf(stream, "PERF: tcache reads=%ld\n", (long)crd);
+      fprintf(stream, "PERF: tcache read misses=%ld (hit ratio=%d%%)\n", (long)cmiss, ratio(cmiss, crd));
+      fprintf(stream, "PERF: tcache bank stalls=%ld (utilization=%d%%)\n", (long)cbank, percent(crd, crd + cbank));
+      fprintf(stream, "PERF: tcache mshr stalls=%ld (utilization=%d%%)\n", (long)cmshr, percent(cmiss, cmiss + cmshr));
+    } break;
+    case VX_DCR_MPM_CLASS_RASTER: {
+      const uint64_t rd = csr(0xB03), lat = csr(0xB04), stl = csr(0xB05);
+      fprintf(stream, "PERF: raster memory reads=%ld\n", (long)rd);
+      fprintf(stream, "PERF: raster memory latency=%d cycles\n", (int)avg(lat, rd));
+      fprintf(stream, "PERF: raster stall cycles=%ld cycles (%d%%)\n", (long)stl, stl ? ratio(stl, total_cycles) : 0);
+      const uint64_t crd = csr(0xB06), cmiss = csr(0xB07), cbank = csr(0xB08), cmshr = csr(0xB09);
+      fprintf(stream, "PERF: rcache reads=%ld\n", (long)crd);
+      fprintf(stream, "PERF: rcache read misses=%ld (hit ratio=%d%%)\n", (long)cmiss, ratio(cmiss, crd));
+      fprintf(stream, "PERF: rcache bank stalls=%ld (utilization=%d%%)\n", (long)cbank, percent(crd, crd + cbank));
+      fprintf(stream, "PERF: rcache mshr stalls=%ld (utilization=%d%%)\n", (long)cmshr, percent(cmiss, cmiss + cmshr));
+    } break;
+    case VX_DCR_MPM_CLASS_OM: {
+      const uint64_t rd = csr(0xB03), wr = csr(0xB04), lat = csr(0xB05), stl = csr(0xB06);
+      fprintf(stream, "PERF: om memory reads=%ld\n", (long)rd);
+      fprintf(stream, "PERF: om memory writes=%ld\n", (long)wr);
+      fprintf(stream, "PERF: om memory latency=%d cycles\n", (int)avg(lat, rd));
+      fprintf(stream, "PERF: om stalls=%ld (%d%%)\n", (long)stl, stl ? ratio(stl, total_cycles) : 0);
+      const uint64_t crd = csr(0xB07), cwr = csr(0xB08), rmiss = csr(0xB09), wmiss = csr(0xB0A), cbank = csr(0xB0B),
+                     cmshr = csr(0xB0C);
+      fprintf(stream, "PERF: ocache reads=%ld\n", (long)crd);
+      fprintf(stream, "PERF: ocache writes=%ld\n", (long)cwr);
+      fprintf(stream, "PERF: ocache read misses=%ld (hit ratio=%d%%)\n", (long)rmiss, ratio(rmiss, crd));
+      fprintf(stream, "PERF: ocache write misses=%ld (hit ratio=%d%%)\n", (long)wmiss, ratio(wmiss, cwr));
+      fprintf(stream, "PERF: ocache bank stalls=%ld (utilization=%d%%)\n", (long)cbank, percent(crd + cwr, crd + cwr + cbank));
+      fprintf(stream, "PERF: ocache mshr stalls=%ld (utilization=%d%%)\n", (long)cmshr,
+              percent(rmiss + wmiss, rmiss + wmiss + cmshr));
+    } break;
+    default:
+      break;
+  }
+  if (perf_class != VX_DCR_MPM_CLASS_NONE) {  // what this back-end counts natively, accumulated over the profiled runs
+    uint64_t t[VX_PERF_COUNT] = {0};
+    if ((err = vx_cuda_perf_totals(hdevice, t, VX_PERF_COUNT)) != 0) return err;
+    const uint64_t rays = t[VX_PERF_RT_PRIMARY] + t[VX_PERF_RT_SHADOW] + t[VX_PERF_RT_BOUNCE];
+    if (rays) {
+      fprintf(stream, "PERF: rt: rays_primary=%ld, rays_shadow=%ld, rays_bounce=%ld, nodes=%ld, tris=%ld, elapsed_ns=%ld\n",
+              (long)t[VX_PERF_RT_PRIMARY], (long)t[VX_PERF_RT_SHADOW], (long)t[VX_PERF_RT_BOUNCE], (long)t[VX_PERF_RT_NODES],
+              (long)t[VX_PERF_RT_TRIS], (long)t[VX_PERF_NS]);
+      fprintf(stream, "PERF: rt: nodes/ray=%f, tris/ray=%f, node bytes=%ld\n", avg(t[VX_PERF_RT_NODES], rays),
+              avg(t[VX_PERF_RT_TRIS], rays), (long)t[VX_PERF_RT_NODE_BYTES]);
+    }
+    if (t[VX_PERF_TILES])
+      fprintf(stream, "PERF: raster: tiles=%ld, quad tests=%ld, fragments=%ld, texels=%ld, elapsed_ns=%ld\n",
+              (long)t[VX_PERF_TILES], (long)t[VX_PERF_TESTS], (long)t[VX_PERF_FRAGMENTS], (long)t[VX_PERF_TEX_READS],
+              (long)t[VX_PERF_NS]);
+    fprintf(stream, "PERF: runs=%ld\n", (long)t[VX_PERF_RUNS]);
+  } else {  // the last run only: its device time and, for the ray tracer, its ray classes
+    uint64_t ns = 0, prim = 0, shadow = 0, bounce = 0;
+    vx_mpm_query(hdevice, VX_CSR_RT_ELAPSED_NS, 0, &ns);
+    if (vx_mpm_query(hdevice, VX_CSR_RT_RAYS_PRIMARY, 0, &prim) == 0 && prim) {
+      vx_mpm_query(hdevice, VX_CSR_RT_RAYS_SHADOW, 0, &shadow);
+      vx_mpm_query(hdevice, VX_CSR_RT_RAYS_BOUNCE, 0, &bounce);
+      fprintf(stream, "PERF: rt: rays_primary=%ld, rays_shadow=%ld, rays_bounce=%ld, elapsed_ns=%ld\n", (long)prim,
+              (long)shadow, (long)bounce, (long)ns);
+      if (ns) fprintf(stream, "PERF: rt: Mrays/s=%f\n", (double)(prim + shadow + bounce) * 1e3 / (double)ns);
+    }
+  }
+  fprintf(stream, "PERF: instrs=%ld, cycles=%ld, IPC=%f\n", (long)total_instrs, (long)max_cycles,
+          (float)avg(total_instrs, max_cycles));
   fflush(stream);
   return 0;
 }

@@ -39,7 +39,8 @@ EXPORTS = [
     "vx_upload_kernel_file", "vx_upload_bytes", "vx_upload_file", "vx_check_occupancy", "vx_dump_perf",
     "vx_dev_init",
 ]
-CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx_cuda_host_unregister"]  # include/vortex_cuda.h
+CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx_cuda_host_unregister",
+                "vx_cuda_perf_totals"]  # include/vortex_cuda.h
 
 _lib = None
 
@@ -75,6 +76,7 @@ def lib():
             "vx_upload_file": [vp, C.c_char_p, C.POINTER(vp)],
             "vx_check_occupancy": [vp, u32, C.POINTER(u32)],
             "vx_cuda_stream": [vp, C.POINTER(vp)], "vx_cuda_device": [vp, C.POINTER(i)],
+            "vx_cuda_perf_totals": [vp, C.POINTER(u64), u32],
         }
         for name, args in sig.items():
             fn = getattr(L, name)
@@ -187,6 +189,12 @@ class Device:
         v = C.c_uint64()
         _check(lib().vx_mpm_query(self.handle, addr, core_id, C.byref(v)), "vx_mpm_query")
         return v.value
+
+    def perf_totals(self):
+        """Accumulated performance-monitor totals, slots VX_PERF_* of include/vortex_cuda.h."""
+        out = (C.c_uint64 * 32)()
+        _check(lib().vx_cuda_perf_totals(self.handle, out, 32), "vx_cuda_perf_totals")
+        return list(out)
 
     def cuda_stream(self):
         """cudaStream_t (as int) that vx_start launches on -- wrap with torch.cuda.ExternalStream."""
