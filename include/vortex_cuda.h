@@ -46,6 +46,26 @@ enum {
 };
 int vx_cuda_perf_totals(vx_device_h hdevice, uint64_t* out, uint32_t count);
 
+/* Triangle setup + tile binning on the device: the role of graphics::Binning (sim/common/gfxutil.cpp:103-276),
+ * which the reference runs on the host, for frames where the host pre-pass and the upload of its output would
+ * dominate.  `vertices` holds srt_vertex_t[num_vertices] (40 B: pos xyzw, color rgba, uv -- CGLTrace::vertex_t)
+ * and `primitives` srt_primitive_t[num_primitives] (3 x u32), both already on the device.  On success
+ * *tilebuf / *primbuf are new buffers (free with vx_mem_free; NULL when empty) holding exactly the bytes
+ * srt_draw3d_binning_rank() produces for the same input (include/skybox_draw3d.h: SRT_TILEBUF_* formats,
+ * rank / num_ranks tile-row dealing).  Returns 0; -1 bad arguments / out of memory / an index past the vertex
+ * buffer; -2 when SRT_TILEBUF_REFERENCE's 16-bit fields would overflow.  Enqueued on the launch stream; waits
+ * once for the output sizes. */
+typedef struct {
+  uint32_t num_tiles, num_prims;
+  uint64_t num_tile_prims; /* sum of pids_count */
+  uint64_t tilebuf_size, primbuf_size;
+  uint32_t format;
+} srt_binning_info_t;
+int vx_cuda_draw3d_binning(vx_device_h hdevice, vx_buffer_h vertices, uint32_t num_vertices, vx_buffer_h primitives,
+                           uint32_t num_primitives, float near_, float far_, uint32_t width, uint32_t height,
+                           uint32_t tile_logsize, uint32_t format, uint32_t rank, uint32_t num_ranks,
+                           vx_buffer_h* tilebuf, vx_buffer_h* primbuf, srt_binning_info_t* info);
+
 /* CUDA device ordinal the handle was opened on. */
 int vx_cuda_device(vx_device_h hdevice, int* ordinal);
 

@@ -35,6 +35,17 @@ class Stats(C.Structure):  # srt_draw3d_stats_t (apps/draw3d/draw3d_app.h)
                 ("bin_ms", C.c_double), ("upload_ms", C.c_double), ("run_ms", C.c_double)]
 
 
+class BinningInfo(C.Structure):  # srt_binning_info_t (include/vortex_cuda.h)
+    _fields_ = [("num_tiles", C.c_uint32), ("num_prims", C.c_uint32), ("num_tile_prims", C.c_uint64),
+                ("tilebuf_size", C.c_uint64), ("primbuf_size", C.c_uint64), ("format", C.c_uint32)]
+
+
+class Drawcall(C.Structure):  # srt_drawcall_t
+    _fields_ = [("states", C.c_uint32 * 24), ("texture_envcolor", C.c_float * 4), ("texture_id", C.c_uint32),
+                ("viewport", C.c_int32 * 4), ("near", C.c_float), ("far", C.c_float), ("num_vertices", C.c_uint32),
+                ("num_primitives", C.c_uint32), ("vertices", C.c_void_p), ("primitives", C.c_void_p)]
+
+
 class TraceStruct(C.Structure):  # srt_trace_t
     _fields_ = [("num_drawcalls", C.c_uint32), ("num_textures", C.c_uint32), ("drawcalls", C.c_void_p),
                 ("textures", C.c_void_p), ("blob", C.c_void_p), ("blob_size", C.c_uint64)]
@@ -113,6 +124,21 @@ class Trace:
     def num_drawcalls(self):
         return self.s.num_drawcalls
 
+    def draw_arrays(self, draw):
+        """-> (vertices f32 [nv, 10], primitives u32 [np, 3], near, far) of one draw call (copies)."""
+        p = host_lib().srt_drawcall_at(C.byref(self.s), draw)
+        if not p:
+            raise IndexError(draw)
+        dc = Drawcall.from_address(p)
+        nv, npr = dc.num_vertices, dc.num_primitives
+        v = np.frombuffer(C.string_at(dc.vertices, nv * 40), np.float32).reshape(nv, 10) if nv else np.zeros((0, 10), np.float32)
+        t = np.frombuffer(C.string_at(dc.primitives, npr * 12), np.uint32).reshape(npr, 3) if npr else np.zeros((0, 3), np.uint32)
+        return v, t, dc.near, dc.far
+
+    def gpu_binning(self, dev, draw, width, height, fmt=TILEBUF_REFERENCE, rank=0, num_ranks=1, tile_logsize=5):
+        """vx_cuda_draw3d_binning on `dev` -> same tuple as binning(), read back from the device buffers."""
+        return gpu_binning(dev, *self.draw_arrays(draw), width, height, fmt, rank, num_ranks, tile_logsize)
+
     def binning(self, draw, width, height, fmt=TILEBUF_REFERENCE, rank=0, num_ranks=1, tile_logsize=5):
         """srt_draw3d_binning_rank -> (num_tiles, tilebuf bytes, primbuf bytes, num_tile_prims)."""
         b = Binning()
@@ -135,6 +161,38 @@ class Trace:
             self.close()
         except Exception:
             pass
+
+
+def gpu_binning(dev, vertices, primitives, near, far, width, height, fmt=TILEBUF_REFERENCE, rank=0, num_ranks=1,
+                tile_logsize=5):
+    """Triangle setup + tile binning on the device (csrc/raster_binning.cu) from host arrays; returns
+    (num_tiles, tilebuf bytes, primbuf bytes, num_tile_prims) like Trace.binning()."""
+    vertices = np.ascontiguousarray(vertices, np.float32)
+    primitives = np.ascontiguousarray(primitives, np.uint32)
+    nv, npr = len(vertices), len(primitives)
+    vb = dev.upload(vertices) if nv else None
+    pb = dev.upload(primitives) if npr else None
+    tb, prb, info = C.c_void_p(), C.c_void_p(), BinningInfo()
+    try:
+        rc = vx.lib().vx_cuda_draw3d_binning(dev.handle, vb.handle if vb else None, nv, pb.handle if pb else None, npr,
+                                             near, far, width, height, tile_logsize, fmt, rank, num_ranks,
+                                             C.byref(tb), C.byref(prb), C.byref(info))
+        if rc != 0:
+            raise vx.VortexError(f"vx_cuda_draw3d_binning failed with code {rc}")
+        tile_bytes = np.zeros(info.tilebuf_size, np.uint8)
+        prim_bytes = np.zeros(info.primbuf_size, np.uint8)
+        if tb:
+            vx.Buffer(dev, tb, info.tilebuf_size).read(tile_bytes)
+        if prb:
+            vx.Buffer(dev, prb, info.primbuf_size).read(prim_bytes)
+        return info.num_tiles, tile_bytes.tobytes(), prim_bytes.tobytes(), info.num_tile_prims
+    finally:
+        for h in (tb, prb):
+            if h:
+                vx.lib().vx_mem_free(h)
+        for b in (vb, pb):
+            if b is not None:
+                b.free()
 
 
 class Draw3D:
