@@ -52,6 +52,8 @@ def parse():
                     help="c1..c5: the RT configs of BASELINE.json; draw3d: the raster path (bench_draw3d.py)")
     ap.add_argument("--trace", default="mouse", help="draw3d: which reference trace (tests/golden/raster/<name>.trc.gz)")
     ap.add_argument("--size", type=int, default=4096, help="draw3d: render target is size x size")
+    ap.add_argument("--gpu-binning", action="store_true",
+                    help="draw3d: e2e leg bins on the device (vx_cuda_draw3d_binning) instead of the host pre-pass")
     ap.add_argument("--ppt", type=int, default=0, help="draw3d diagnostic: force pixels per thread (4 or 1; 0 = by grid size)")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel, 2 wide while-while")

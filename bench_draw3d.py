@@ -202,7 +202,8 @@ def native_arm(args, ClockSampler, load_peaks):
 
     # ---- e2e: the reference app's loop with host buffers, wall clock -------------------------------
     host_frame = torch.empty(H * W, dtype=torch.int32).pin_memory()
-    app2 = d3.Draw3D(W, H, flags=ALL_SW | d3.WIDE_TILES, rank=rank, num_ranks=world, device=dev)
+    app2 = d3.Draw3D(W, H, flags=ALL_SW | d3.WIDE_TILES | (d3.GPU_BINNING if getattr(args, "gpu_binning", False) else 0),
+                     rank=rank, num_ranks=world, device=dev)
     c2addr, _ = app2.buffer_addresses()
     cbuf2 = torch.as_tensor(DevMem(c2addr, W * H * 4), device="cuda").view(H, W)
 
@@ -282,7 +283,8 @@ def native_arm(args, ClockSampler, load_peaks):
                                      "one NCCL gather per frame") if world > 1 else "single GPU"},
             "e2e": {"value": frags_total / e2e_s / 1e6, "unit": "Mfragments/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_s * 1e3,
-                    "host_ms": {"binning": st2["bin_ms"], "upload": st2["upload_ms"], "start+wait": st2["run_ms"]}},
+                    "host_ms": {"binning": st2["bin_ms"], "upload": st2["upload_ms"], "start+wait": st2["run_ms"]},
+                    "binning": "device" if getattr(args, "gpu_binning", False) else "host"},
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "kernel": "raster_tile_kernel (all draws of a frame)",

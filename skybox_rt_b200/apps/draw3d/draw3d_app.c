@@ -288,26 +288,60 @@ static int stage_draw(srt_draw3d_t* r, const srt_trace_t* trace, const srt_drawc
                       uint64_t addr[3], uint32_t* num_tiles) {
   srt_binning_t b;
   double t0 = now_ms(), t1;
-  int rc = srt_draw3d_binning_rank(dc, r->width, r->height, RASTER_TILE_LOGSIZE, tile_format(r), r->rank, r->num_ranks, &b);
-  if (rc != 0) {
-    printf("Error: binning failed (%d)%s\n", rc, rc == -2 ? ": 16-bit tile headers overflow, use wide tiles" : "");
-    return rc;
-  }
-  t1 = now_ms();
-  r->stats.bin_ms += t1 - t0;
-  *num_tiles = b.num_tiles;
+  int rc;
   *tex_out = NULL;
-  if (b.num_tiles == 0) { srt_binning_free(&b); return 0; } /* main.cpp:190-191 */
-  if (*tile_buffer) vx_mem_free(*tile_buffer);
-  if (*prim_buffer) vx_mem_free(*prim_buffer);
-  *tile_buffer = *prim_buffer = NULL;
-  rc = vx_mem_alloc(r->device, b.tilebuf_size, VX_MEM_READ, tile_buffer) || vx_mem_address(*tile_buffer, &addr[0]) ||
-       vx_mem_alloc(r->device, b.primbuf_size, VX_MEM_READ, prim_buffer) || vx_mem_address(*prim_buffer, &addr[1]) ||
-       vx_copy_to_dev(*tile_buffer, b.tilebuf, 0, b.tilebuf_size) || vx_copy_to_dev(*prim_buffer, b.primbuf, 0, b.primbuf_size);
-  r->stats.h2d_bytes += b.tilebuf_size + b.primbuf_size;
-  r->stats.prims += b.num_prims; r->stats.tiles += b.num_tiles; r->stats.tile_prims += b.num_tile_prims;
-  r->stats.draws_submitted += 1;
-  srt_binning_free(&b);
+  if (r->flags & SRT_DRAW3D_GPU_BINNING) {
+    /* the pre-pass on the device: upload the draw's vertices and indices instead of its binned form */
+    vx_buffer_h vb = NULL, ib = NULL;
+    srt_binning_info_t info;
+    const uint64_t vbytes = (uint64_t)dc->num_vertices * sizeof(srt_vertex_t), ibytes = (uint64_t)dc->num_primitives * sizeof(srt_primitive_t);
+    *num_tiles = 0;
+    if (dc->num_primitives == 0 || dc->num_vertices == 0) return 0;
+    if (*tile_buffer) vx_mem_free(*tile_buffer);
+    if (*prim_buffer) vx_mem_free(*prim_buffer);
+    *tile_buffer = *prim_buffer = NULL;
+    rc = vx_upload_bytes(r->device, dc->vertices, vbytes, &vb) || vx_upload_bytes(r->device, dc->primitives, ibytes, &ib);
+    t1 = now_ms();
+    r->stats.upload_ms += t1 - t0;
+    if (rc == 0)
+      rc = vx_cuda_draw3d_binning(r->device, vb, dc->num_vertices, ib, dc->num_primitives, dc->viewport.near_, dc->viewport.far_,
+                                  r->width, r->height, RASTER_TILE_LOGSIZE, tile_format(r), r->rank, r->num_ranks, tile_buffer,
+                                  prim_buffer, &info);
+    vx_mem_free(vb);
+    vx_mem_free(ib);
+    if (rc != 0) {
+      printf("Error: binning failed (%d)%s\n", rc, rc == -2 ? ": 16-bit tile headers overflow, use wide tiles" : "");
+      return rc;
+    }
+    r->stats.bin_ms += now_ms() - t1;
+    t1 = now_ms();
+    *num_tiles = info.num_tiles;
+    if (info.num_tiles == 0) return 0;
+    rc = vx_mem_address(*tile_buffer, &addr[0]) || vx_mem_address(*prim_buffer, &addr[1]);
+    r->stats.h2d_bytes += vbytes + ibytes;
+    r->stats.prims += info.num_prims; r->stats.tiles += info.num_tiles; r->stats.tile_prims += info.num_tile_prims;
+    r->stats.draws_submitted += 1;
+  } else {
+    rc = srt_draw3d_binning_rank(dc, r->width, r->height, RASTER_TILE_LOGSIZE, tile_format(r), r->rank, r->num_ranks, &b);
+    if (rc != 0) {
+      printf("Error: binning failed (%d)%s\n", rc, rc == -2 ? ": 16-bit tile headers overflow, use wide tiles" : "");
+      return rc;
+    }
+    t1 = now_ms();
+    r->stats.bin_ms += t1 - t0;
+    *num_tiles = b.num_tiles;
+    if (b.num_tiles == 0) { srt_binning_free(&b); return 0; } /* main.cpp:190-191 */
+    if (*tile_buffer) vx_mem_free(*tile_buffer);
+    if (*prim_buffer) vx_mem_free(*prim_buffer);
+    *tile_buffer = *prim_buffer = NULL;
+    rc = vx_mem_alloc(r->device, b.tilebuf_size, VX_MEM_READ, tile_buffer) || vx_mem_address(*tile_buffer, &addr[0]) ||
+         vx_mem_alloc(r->device, b.primbuf_size, VX_MEM_READ, prim_buffer) || vx_mem_address(*prim_buffer, &addr[1]) ||
+         vx_copy_to_dev(*tile_buffer, b.tilebuf, 0, b.tilebuf_size) || vx_copy_to_dev(*prim_buffer, b.primbuf, 0, b.primbuf_size);
+    r->stats.h2d_bytes += b.tilebuf_size + b.primbuf_size;
+    r->stats.prims += b.num_prims; r->stats.tiles += b.num_tiles; r->stats.tile_prims += b.num_tile_prims;
+    r->stats.draws_submitted += 1;
+    srt_binning_free(&b);
+  }
   if (rc == 0 && dc->states.texture_enabled) {
     const srt_texture_t* tex = srt_trace_texture(trace, dc->texture_id);
     uint64_t level0;

@@ -18,19 +18,19 @@
 static const char* trace_file = "triangle.trc.gz";
 static const char* output_file = "output.png";
 static const char* reference_file = NULL;
-static int sw_rast = 0, sw_tex = 0, sw_om = 0, wide = 0;
+static int sw_rast = 0, sw_tex = 0, sw_om = 0, wide = 0, gpu_binning = 0;
 static uint32_t start_draw = 0, end_draw = 0xffffffffu;
 static uint32_t dst_width = 128, dst_height = 128;
 
 static void show_usage(void) {
   printf("Vortex 3D Rendering Test.\n");
   printf("Usage: [-t trace] [-s startdraw] [-e enddraw] [-o output] [-r reference] [-w width] [-h height] "
-         "[-x s/w rast] [-y s/w om] [-u s/w tex] [-W wide tile headers]\n");
+         "[-x s/w rast] [-y s/w om] [-u s/w tex] [-W wide tile headers] [-g binning on the GPU]\n");
 }
 
 static void parse_args(int argc, char** argv) {
   int c;
-  while ((c = getopt(argc, argv, "t:s:e:o:r:w:h:k:uxyzW?")) != -1) {
+  while ((c = getopt(argc, argv, "t:s:e:o:r:w:h:k:uxyzWg?")) != -1) {
     switch (c) {
     case 't': trace_file = optarg; break;
     case 's': start_draw = (uint32_t)atoi(optarg); break;
@@ -43,6 +43,7 @@ static void parse_args(int argc, char** argv) {
     case 'x': sw_rast = 1; break;
     case 'y': sw_om = 1; break;
     case 'W': wide = 1; break;
+    case 'g': gpu_binning = 1; break;
     case 'k':
       if (atoi(optarg) != RASTER_TILE_LOGSIZE) {
         printf("Error: the tile size is fixed at 2^%d on this back-end\n", RASTER_TILE_LOGSIZE);
@@ -87,7 +88,8 @@ int main(int argc, char* argv[]) {
   printf("upload program\n");
   rc = srt_draw3d_open(device, dst_width, dst_height,
                        (sw_rast ? SRT_DRAW3D_SW_RAST : 0) | (sw_om ? SRT_DRAW3D_SW_OM : 0) |
-                           (sw_tex ? SRT_DRAW3D_SW_TEX : 0) | (wide ? SRT_DRAW3D_WIDE_TILES : 0),
+                           (sw_tex ? SRT_DRAW3D_SW_TEX : 0) | (wide ? SRT_DRAW3D_WIDE_TILES : 0) |
+                               (gpu_binning ? SRT_DRAW3D_GPU_BINNING : 0),
                        0, 1, &app);
   if (rc == 0) {
     printf("clear depth buffer\nclear destination buffer\n");

@@ -7,12 +7,16 @@
 // vectors on the host; here the same result comes from passes that have no order dependence except two
 // prefix sums and a per-tile sort:
 //
-//   setup      thread / triangle   edge equations, attribute planes, tile rectangle, keep flag
+//   setup      thread / triangle   edge equations, attribute planes, tile rectangle, keep flag; records leave
+//                                  the CTA through shared memory as one coalesced block
 //   scan       keep flags -> primitive ids (order preserving compaction)
-//   count      warp / triangle     record -> primbuf[pid]; atomicAdd on a dense (tile_x, tile_y) grid
+//   count      lane / triangle     atomicAdd on a dense (tile_x, tile_y) grid; a triangle over more than 8
+//                                  tiles is walked by its whole warp
 //   scan       grid counts -> start of every tile's id list, non-empty flags -> tile index
+//   (one 28-byte read-back: the sizes of the two outputs are data)
+//   compact    thread / word       kept records -> primbuf[pid]
 //   headers    thread / grid cell
-//   fill       warp / triangle     pid into its tiles' lists (atomic cursor: arrival order)
+//   fill       lane / triangle     pid into its tiles' lists (atomic cursor: arrival order)
 //   sort       CTA / tile          ascending pid = submission order (bitonic, shared or global memory)
 //
 // Float expressions keep the host file's operation order; the library is built with -fmad=false and IEEE
@@ -52,23 +56,44 @@ __device__ __forceinline__ V4 to_screen(V4 c, const BinParams& P) {  // math.hpp
   const float rhw = (c.w != 0.0f) ? (1.0f / c.w) : 0.0f;
   return V4{(c.x * rhw) * P.scale_x + P.min_x, (c.y * rhw) * P.scale_y + P.min_y, (c.z * rhw) * P.scale_z + P.min_z, rhw};
 }
-__device__ __forceinline__ void plane(int32_t* d, float a0, float a1, float a2) {  // ATTRIBUTE_DELTA, gfxutil.cpp:189-192
-  d[0] = to_fixed(a0 - a2, 16777216.0f);
-  d[1] = to_fixed(a1 - a2, 16777216.0f);
-  d[2] = to_fixed(a2, 16777216.0f);
+template <class Rec>
+__device__ __forceinline__ void plane(Rec rec, int w, uint32_t t, float a0, float a1, float a2) {  // ATTRIBUTE_DELTA, gfxutil.cpp:189-192
+  rec[w + 0][t] = to_fixed(a0 - a2, 16777216.0f);
+  rec[w + 1][t] = to_fixed(a1 - a2, 16777216.0f);
+  rec[w + 2][t] = to_fixed(a2, 16777216.0f);
 }
 
 // ---- setup: one thread per submitted triangle -------------------------------------------------------
-__global__ void __launch_bounds__(128) bin_setup_kernel(const BinParams P, int32_t* __restrict__ tmp_prims,
-                                                        TileRect* __restrict__ rects, uint32_t* __restrict__ keep,
-                                                        uint32_t* __restrict__ error) {
-  const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= P.num_primitives) return;
-  keep[n] = 0;
+// Each thread builds its record in shared memory ([word][thread]: conflict-free); the CTA then writes its 128
+// records to tmp_prims as one contiguous, coalesced block.
+constexpr int kSetupThreads = 128;
+
+__device__ __forceinline__ bool setup_one(const BinParams& P, uint32_t n, int32_t (*rec)[kSetupThreads], TileRect* rect,
+                                          uint32_t* error);
+
+__global__ void __launch_bounds__(kSetupThreads) bin_setup_kernel(const BinParams P, int32_t* __restrict__ tmp_prims,
+                                                                  TileRect* __restrict__ rects, uint32_t* __restrict__ keep,
+                                                                  uint32_t* __restrict__ error) {
+  __shared__ int32_t s_rec[30][kSetupThreads];
+  const uint32_t first = blockIdx.x * kSetupThreads, n = first + threadIdx.x;
+  if (n < P.num_primitives) {
+    TileRect r = {0, 0, 0, 0};
+    const bool k = setup_one(P, n, s_rec, &r, error);
+    keep[n] = k ? 1u : 0u;
+    rects[n] = r;
+  }
+  __syncthreads();
+  const uint32_t in_cta = min((uint32_t)kSetupThreads, P.num_primitives - first);
+  int32_t* dst = tmp_prims + (size_t)first * 30;
+  for (uint32_t w = threadIdx.x; w < in_cta * 30; w += kSetupThreads) dst[w] = s_rec[w % 30][w / 30];
+}
+
+__device__ __forceinline__ bool setup_one(const BinParams& P, uint32_t n, int32_t (*rec)[kSetupThreads], TileRect* rect,
+                                          uint32_t* error) {
   const srt_primitive_t tri = P.primitives[n];
   if (tri.i0 >= P.num_vertices || tri.i1 >= P.num_vertices || tri.i2 >= P.num_vertices) {
     atomicOr(error, 1u);  // the host loader refuses such a trace; never read out of bounds
-    return;
+    return false;
   }
   const srt_vertex_t *v0 = P.vertices + tri.i0, *v1 = P.vertices + tri.i1, *v2 = P.vertices + tri.i2;
   const V4 c0 = load_pos8(v0), c1 = load_pos8(v1), c2 = load_pos8(v2);
@@ -85,7 +110,7 @@ __global__ void __launch_bounds__(128) bin_setup_kernel(const BinParams P, int32
   e[1][2] = (h2.x * h0.y) - (h0.x * h2.y);
   e[2][2] = (h0.x * h1.y) - (h1.x * h0.y);
   const float det = e[0][2] * h0.w + e[1][2] * h1.w + e[2][2] * h2.w;
-  if (det == 0) return;  // degenerate, gfxutil.cpp:139-143
+  if (det == 0) return false;  // degenerate, gfxutil.cpp:139-143
   if (det < 0) {
 #pragma unroll
     for (int i = 0; i < 3; ++i) { e[i][0] *= -1.0f; e[i][1] *= -1.0f; e[i][2] *= -1.0f; }
@@ -96,7 +121,7 @@ __global__ void __launch_bounds__(128) bin_setup_kernel(const BinParams P, int32
   const int t = x86_cvtt(floorf(min_f(s0.y, min_f(s1.y, s2.y)))), b = x86_cvtt(ceilf(max_f(s0.y, max_f(s1.y, s2.y))));
   const uint32_t left = (uint32_t)(l > 0 ? l : 0), right = (uint32_t)(r < (int)P.width ? r : (int)P.width);
   const uint32_t top = (uint32_t)(t > 0 ? t : 0), bottom = (uint32_t)(b < (int)P.height ? b : (int)P.height);
-  if (right <= left || bottom <= top) return;
+  if (right <= left || bottom <= top) return false;
 #pragma unroll
   for (int i = 0; i < 3; ++i) e[i][2] += e[i][0] * 0.5f + e[i][1] * 0.5f;  // pixel centres, :195-198
   // normalise by the largest |a|, |b| and convert to 16.16 (gfxutil.cpp:79-96)
@@ -104,18 +129,18 @@ __global__ void __launch_bounds__(128) bin_setup_kernel(const BinParams P, int32
   m = max_f(m, fabsf(e[1][0])); m = max_f(m, fabsf(e[2][0]));
   m = max_f(m, fabsf(e[0][1])); m = max_f(m, fabsf(e[1][1])); m = max_f(m, fabsf(e[2][1]));
   const float scale = 1.0f / m;
-  int32_t* out = tmp_prims + (size_t)n * 30;
+  const uint32_t t_ = threadIdx.x;
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
-    out[3 * i + 0] = to_fixed(e[i][0] * scale, 65536.0f);
-    out[3 * i + 1] = to_fixed(e[i][1] * scale, 65536.0f);
-    out[3 * i + 2] = to_fixed(e[i][2] * scale, 65536.0f);
+    rec[3 * i + 0][t_] = to_fixed(e[i][0] * scale, 65536.0f);
+    rec[3 * i + 1][t_] = to_fixed(e[i][1] * scale, 65536.0f);
+    rec[3 * i + 2][t_] = to_fixed(e[i][2] * scale, 65536.0f);
   }
-  plane(out + 9, s0.z, s1.z, s2.z);
+  plane(rec, 9, t_, s0.z, s1.z, s2.z);
 #pragma unroll
-  for (int k = 0; k < 4; ++k) plane(out + 12 + 3 * k, v0->color[k], v1->color[k], v2->color[k]);
-  plane(out + 24, v0->texcoord[0], v1->texcoord[0], v2->texcoord[0]);
-  plane(out + 27, v0->texcoord[1], v1->texcoord[1], v2->texcoord[1]);
+  for (int k = 0; k < 4; ++k) plane(rec, 12 + 3 * k, t_, v0->color[k], v1->color[k], v2->color[k]);
+  plane(rec, 24, t_, v0->texcoord[0], v1->texcoord[0], v2->texcoord[0]);
+  plane(rec, 27, t_, v0->texcoord[1], v1->texcoord[1], v2->texcoord[1]);
   // tiles touched (gfxutil.cpp:221-235), clamped to the grid exactly as the host pre-pass does
   const uint32_t tile = 1u << P.L;
   uint32_t tx0 = left >> P.L, tx1 = (right + tile - 1) >> P.L, ty0 = top >> P.L, ty1 = (bottom + tile - 1) >> P.L;
@@ -125,8 +150,8 @@ __global__ void __launch_bounds__(128) bin_setup_kernel(const BinParams P, int32
   if (ty1 > P.tiles_y) ty1 = P.tiles_y;
   if (tx0 > tx1) tx0 = tx1;
   if (ty0 > ty1) ty0 = ty1;
-  rects[n] = TileRect{(uint16_t)tx0, (uint16_t)tx1, (uint16_t)ty0, (uint16_t)ty1};
-  keep[n] = 1;
+  *rect = TileRect{(uint16_t)tx0, (uint16_t)tx1, (uint16_t)ty0, (uint16_t)ty1};
+  return true;
 }
 
 // ---- exclusive scan of (v, v != 0) over a u32 array: reduce / spine / apply ---------------------------
@@ -214,27 +239,59 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint32_t
   }
 }
 
-// ---- count: one warp per submitted triangle -----------------------------------------------------------
-__global__ void __launch_bounds__(256) bin_count_kernel(const BinParams P, const int32_t* __restrict__ tmp_prims,
-                                                        const TileRect* __restrict__ rects, const uint32_t* __restrict__ keep,
-                                                        const uint2* __restrict__ pid_of, int32_t* __restrict__ primbuf,
+// ---- count / fill: one lane per submitted triangle; a triangle touching many tiles is shared by its warp ----
+constexpr uint32_t kLaneCells = 8;  // rectangles up to this many tiles are walked by the owning lane alone
+
+// Calls visit(tx, ty, pid) once for every tile of every kept triangle of this warp's 32 triangles.
+template <class Visit>
+__device__ __forceinline__ void for_each_tile(const BinParams& P, const TileRect* __restrict__ rects,
+                                              const uint32_t* __restrict__ keep, const uint2* __restrict__ pid_of, Visit visit) {
+  const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+  const bool valid = n < P.num_primitives && keep[n] != 0;
+  uint32_t xs = 0, ys = 0, pid = 0, cells = 0;
+  if (valid) {
+    const uint2 r = *reinterpret_cast<const uint2*>(rects + n);  // (tx0 | tx1 << 16, ty0 | ty1 << 16)
+    xs = r.x; ys = r.y;
+    pid = pid_of[n].x;
+    cells = ((xs >> 16) - (xs & 0xffff)) * ((ys >> 16) - (ys & 0xffff));
+  }
+  if (valid && cells <= kLaneCells) {
+    const uint32_t h = (ys >> 16) - (ys & 0xffff);
+    for (uint32_t c = 0; c < cells; ++c) visit((xs & 0xffff) + c / h, (ys & 0xffff) + c % h, pid);
+  }
+  uint32_t big = __ballot_sync(0xffffffffu, valid && cells > kLaneCells);
+  while (big) {
+    const int src = __ffs(big) - 1;
+    big &= big - 1;
+    const uint32_t bx = __shfl_sync(0xffffffffu, xs, src), by = __shfl_sync(0xffffffffu, ys, src);
+    const uint32_t bpid = __shfl_sync(0xffffffffu, pid, src), bcells = __shfl_sync(0xffffffffu, cells, src);
+    const uint32_t h = (by >> 16) - (by & 0xffff);
+    for (uint32_t c = lane; c < bcells; c += 32) visit((bx & 0xffff) + c / h, (by & 0xffff) + c % h, bpid);
+  }
+}
+
+__global__ void __launch_bounds__(256) bin_count_kernel(const BinParams P, const TileRect* __restrict__ rects,
+                                                        const uint32_t* __restrict__ keep, const uint2* __restrict__ pid_of,
                                                         uint32_t* __restrict__ count, unsigned long long* __restrict__ pairs) {
-  const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (n >= P.num_primitives || !keep[n]) return;
-  const uint32_t pid = pid_of[n].x;
-  if (lane < 30) primbuf[(size_t)pid * 30 + lane] = tmp_prims[(size_t)n * 30 + lane];
-  const TileRect r = rects[n];
-  const uint32_t w = r.tx1 - r.tx0, h = r.ty1 - r.ty0, cells = w * h;
   uint32_t mine = 0;
-  for (uint32_t c = lane; c < cells; c += 32) {
-    const uint32_t tx = r.tx0 + c / h, ty = r.ty0 + c % h;
+  for_each_tile(P, rects, keep, pid_of, [&](uint32_t tx, uint32_t ty, uint32_t) {
     if (ty % P.num_ranks == P.rank) {
       atomicAdd(count + (size_t)tx * P.tiles_y + ty, 1u);
       ++mine;
     }
-  }
-  mine = __reduce_add_sync(0xffffffffu, mine);  // the whole warp is here: n and keep[n] are warp-uniform
-  if (lane == 0 && mine) atomicAdd(pairs, (unsigned long long)mine);  // 64-bit total: the u32 scan may wrap
+  });
+  mine = __reduce_add_sync(0xffffffffu, mine);
+  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(pairs, (unsigned long long)mine);  // 64-bit total: the u32 scan may wrap
+}
+
+// ---- compact: kept records -> primbuf[pid], one thread per 8-byte word (coalesced both ways) ---------------
+__global__ void __launch_bounds__(256) bin_compact_kernel(const uint2* __restrict__ tmp_prims, const uint32_t* __restrict__ keep,
+                                                          const uint2* __restrict__ pid_of, uint32_t num_words,
+                                                          uint2* __restrict__ primbuf) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;  // 15 words per 120-byte record
+  if (w >= num_words) return;
+  const uint32_t n = w / 15u, j = w - n * 15u;
+  if (keep[n]) primbuf[(size_t)pid_of[n].x * 15 + j] = tmp_prims[w];
 }
 
 // ---- headers: one thread per grid cell, x-major like std::map<pair<tile_x, tile_y>> (gfxutil.cpp:243-262)
@@ -260,22 +317,16 @@ __global__ void __launch_bounds__(256) bin_headers_kernel(const BinParams P, con
   }
 }
 
-// ---- fill: one warp per submitted triangle, arrival order inside a tile ----------------------------------
+// ---- fill: pid into its tiles' lists, arrival order inside a tile (sorted afterwards) ------------------------
 __global__ void __launch_bounds__(256) bin_fill_kernel(const BinParams P, const TileRect* __restrict__ rects,
                                                        const uint32_t* __restrict__ keep, const uint2* __restrict__ pid_of,
                                                        const uint2* __restrict__ cursor, uint32_t* __restrict__ fill,
                                                        uint32_t* __restrict__ pids) {
-  const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (n >= P.num_primitives || !keep[n]) return;
-  const uint32_t pid = pid_of[n].x;
-  const TileRect r = rects[n];
-  const uint32_t w = r.tx1 - r.tx0, h = r.ty1 - r.ty0, cells = w * h;
-  for (uint32_t c = lane; c < cells; c += 32) {
-    const uint32_t tx = r.tx0 + c / h, ty = r.ty0 + c % h;
-    if (ty % P.num_ranks != P.rank) continue;
+  for_each_tile(P, rects, keep, pid_of, [&](uint32_t tx, uint32_t ty, uint32_t pid) {
+    if (ty % P.num_ranks != P.rank) return;
     const size_t g = (size_t)tx * P.tiles_y + ty;
     pids[cursor[g].x + atomicAdd(fill + g, 1u)] = pid;
-  }
+  });
 }
 
 // ---- sort: one CTA per grid cell; ascending pid = the reference's submission order ------------------------
@@ -335,20 +386,21 @@ int scan_u32(cudaStream_t s, const uint32_t* in, uint32_t n, uint2* block_sums, 
   return 0;
 }
 
-struct Scratch {  // stream-ordered temporaries of one call
+// One stream-ordered allocation per call, carved into 256-byte aligned pieces; the pieces that must start at zero
+// come first and are cleared with one memset.
+struct Scratch {
   cudaStream_t s;
-  void* p[16];
-  int n = 0;
+  uint8_t* base = nullptr;
+  size_t used = 0, planned = 0;
   explicit Scratch(cudaStream_t st) : s(st) {}
-  ~Scratch() { for (int i = 0; i < n; ++i) cudaFreeAsync(p[i], s); }
-  template <class T>
-  T* get(size_t count, bool zero) {
-    void* q = nullptr;
-    const size_t bytes = (count ? count : 1) * sizeof(T);
-    if (cudaMallocAsync(&q, bytes, s) != cudaSuccess) return nullptr;
-    p[n++] = q;
-    if (zero && cudaMemsetAsync(q, 0, bytes, s) != cudaSuccess) return nullptr;
-    return static_cast<T*>(q);
+  ~Scratch() { if (base) cudaFreeAsync(base, s); }
+  static size_t pad(size_t bytes) { return (bytes + 255) & ~(size_t)255; }
+  template <class T> void plan(size_t count) { planned += pad((count ? count : 1) * sizeof(T)); }
+  bool commit() { return cudaMallocAsync((void**)&base, planned, s) == cudaSuccess; }
+  template <class T> T* take(size_t count) {
+    T* q = reinterpret_cast<T*>(base + used);
+    used += pad((count ? count : 1) * sizeof(T));
+    return q;
   }
 };
 
@@ -397,26 +449,32 @@ extern "C" int vx_cuda_draw3d_binning(vx_device_h hdevice, vx_buffer_h hvertices
   const uint32_t scan_blocks = ((np > ngrid ? np : ngrid) + kScanTile - 1) / kScanTile;
 
   Scratch tmp(s);
-  int32_t* tmp_prims = tmp.get<int32_t>((size_t)np * 30, false);
-  TileRect* rects = tmp.get<TileRect>(np, false);
-  uint32_t* keep = tmp.get<uint32_t>(np, false);
-  uint2* pid_of = tmp.get<uint2>(np, false);
-  uint32_t* count = tmp.get<uint32_t>(ngrid, true);
-  uint32_t* fill = tmp.get<uint32_t>(ngrid, true);
-  uint2* cursor = tmp.get<uint2>(ngrid, false);
-  uint2* block_sums = tmp.get<uint2>(scan_blocks, false);
-  uint2* totals = tmp.get<uint2>(2, true);   // [0] kept primitives, [1] (pairs, non-empty tiles)
-  uint32_t* error = tmp.get<uint32_t>(1, true);
-  unsigned long long* pairs = tmp.get<unsigned long long>(1, true);
-  int32_t* prims_full = tmp.get<int32_t>((size_t)np * 30, false);  // compacted records before the exact-size buffer exists
-  if (!tmp_prims || !rects || !keep || !pid_of || !count || !fill || !cursor || !block_sums || !totals || !error || !pairs || !prims_full) {
+  tmp.plan<uint32_t>(ngrid); tmp.plan<uint32_t>(ngrid); tmp.plan<uint2>(2); tmp.plan<uint32_t>(1);
+  tmp.plan<unsigned long long>(1);
+  const size_t zeroed = tmp.planned;
+  tmp.plan<int32_t>((size_t)np * 30); tmp.plan<TileRect>(np); tmp.plan<uint32_t>(np); tmp.plan<uint2>(np);
+  tmp.plan<uint2>(ngrid); tmp.plan<uint2>(scan_blocks);
+  if (!tmp.commit()) {
+    cudaGetLastError();
     fprintf(stderr, "[VXDRV] draw3d binning: out of device memory\n");
     return -1;
   }
-  bin_setup_kernel<<<(np + 127) / 128, 128, 0, s>>>(P, tmp_prims, rects, keep, error);
+  uint32_t* count = tmp.take<uint32_t>(ngrid);
+  uint32_t* fill = tmp.take<uint32_t>(ngrid);
+  uint2* totals = tmp.take<uint2>(2);   // [0] kept primitives, [1] (pairs, non-empty tiles)
+  uint32_t* error = tmp.take<uint32_t>(1);
+  unsigned long long* pairs = tmp.take<unsigned long long>(1);
+  VX_CUDA_OK(cudaMemsetAsync(tmp.base, 0, zeroed, s));
+  int32_t* tmp_prims = tmp.take<int32_t>((size_t)np * 30);
+  TileRect* rects = tmp.take<TileRect>(np);
+  uint32_t* keep = tmp.take<uint32_t>(np);
+  uint2* pid_of = tmp.take<uint2>(np);
+  uint2* cursor = tmp.take<uint2>(ngrid);
+  uint2* block_sums = tmp.take<uint2>(scan_blocks);
+  bin_setup_kernel<<<(np + kSetupThreads - 1) / kSetupThreads, kSetupThreads, 0, s>>>(P, tmp_prims, rects, keep, error);
   if (scan_u32(s, keep, np, block_sums, pid_of, totals + 0) != 0) return -1;
-  const uint32_t warp_blocks = (uint32_t)(((uint64_t)np * 32 + 255) / 256);
-  bin_count_kernel<<<warp_blocks, 256, 0, s>>>(P, tmp_prims, rects, keep, pid_of, prims_full, count, pairs);
+  const uint32_t prim_blocks = (np + 255) / 256;
+  bin_count_kernel<<<prim_blocks, 256, 0, s>>>(P, rects, keep, pid_of, count, pairs);
   if (scan_u32(s, count, ngrid, block_sums, cursor, totals + 1) != 0) return -1;
   VX_CUDA_OK(cudaGetLastError());
   // the sizes of the two outputs are data: one small read-back
@@ -442,7 +500,9 @@ extern "C" int vx_cuda_draw3d_binning(vx_device_h hdevice, vx_buffer_h hvertices
   vx_buffer_h tb = nullptr, prb = nullptr;
   if (num_prims) {
     if (vx_mem_alloc(hdevice, info->primbuf_size, VX_MEM_READ, &prb) != 0) return -1;
-    VX_CUDA_OK(cudaMemcpyAsync(static_cast<vx_buffer*>(prb)->dptr, prims_full, info->primbuf_size, cudaMemcpyDeviceToDevice, s));
+    const uint32_t words = np * 15u;  // np <= 2^27
+    bin_compact_kernel<<<(words + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(tmp_prims), keep, pid_of, words,
+                                                           static_cast<uint2*>(static_cast<vx_buffer*>(prb)->dptr));
   }
   if (num_tiles) {
     if (vx_mem_alloc(hdevice, info->tilebuf_size, VX_MEM_READ, &tb) != 0) {
@@ -452,7 +512,7 @@ extern "C" int vx_cuda_draw3d_binning(vx_device_h hdevice, vx_buffer_h hvertices
     uint8_t* tilebuf = static_cast<uint8_t*>(static_cast<vx_buffer*>(tb)->dptr);
     uint32_t* pids = reinterpret_cast<uint32_t*>(tilebuf + (size_t)num_tiles * hdr);
     bin_headers_kernel<<<(ngrid + 255) / 256, 256, 0, s>>>(P, count, cursor, num_tiles, tilebuf, error);
-    bin_fill_kernel<<<warp_blocks, 256, 0, s>>>(P, rects, keep, pid_of, cursor, fill, pids);
+    bin_fill_kernel<<<prim_blocks, 256, 0, s>>>(P, rects, keep, pid_of, cursor, fill, pids);
     bin_sort_kernel<<<ngrid, 256, 0, s>>>(count, cursor, pids);
     VX_CUDA_OK(cudaGetLastError());
     if (format == SRT_TILEBUF_REFERENCE) {  // a 16-bit header field may not hold the value: -2, like the host pre-pass

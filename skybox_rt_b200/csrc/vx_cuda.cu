@@ -46,9 +46,13 @@ void unlink_buffer(vx_buffer* b) {
   d->bytes_used -= b->size;
 }
 
+// Buffers come from the device's stream-ordered pool (cudaMallocAsync on the launch stream, release threshold
+// raised in vx_dev_open): an allocation is a pool hit instead of a driver call, and a free is ordered behind
+// the kernels and copies already queued, so vx_mem_free does not have to wait for them.  The per-draw
+// alloc / upload / free pattern of the reference's apps (draw3d/main.cpp:198-211, :346) costs microseconds.
 int destroy_buffer(vx_buffer* b) {
   unlink_buffer(b);
-  cudaError_t e = cudaFree(b->dptr);
+  cudaError_t e = cudaFreeAsync(b->dptr, b->dev->stream);
   free(b->shadow);
   delete b;
   return e == cudaSuccess ? 0 : -1;
@@ -57,9 +61,9 @@ int destroy_buffer(vx_buffer* b) {
 int alloc_buffer(vx_device* dev, uint64_t size, int flags, uint64_t reported, vx_buffer** out) {
   void* p = nullptr;
   VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
-  VX_CUDA_OK(cudaMalloc(&p, size));
+  VX_CUDA_OK(cudaMallocAsync(&p, size, dev->stream));
   vx_buffer* b = new (std::nothrow) vx_buffer();
-  if (!b) { cudaFree(p); return -1; }
+  if (!b) { cudaFreeAsync(p, dev->stream); return -1; }
   b->dev = dev;
   b->dptr = p;
   b->size = size;
@@ -120,6 +124,13 @@ int vx_dev_open(vx_device_h* hdevice) {
     delete dev;
     return -1;
   }
+  {  // stream-ordered temporaries (raster_binning.cu) stay in the pool between calls instead of going back to the OS
+    cudaMemPool_t pool;
+    uint64_t keep = ~0ull;
+    if (cudaDeviceGetDefaultMemPool(&pool, ordinal) == cudaSuccess)
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    cudaGetLastError();
+  }
   *hdevice = dev;
   return 0;
 }
@@ -133,6 +144,7 @@ int vx_dev_close(vx_device_h hdevice) {
   srt::rt_destroy(dev);
   srt::raster_destroy(dev);
   while (dev->buffers) destroy_buffer(dev->buffers);  // apps leak their per-draw args buffers
+  cudaStreamSynchronize(dev->stream);                 // the frees are stream-ordered
   cudaEventDestroy(dev->ev_start);
   cudaEventDestroy(dev->ev_stop);
   cudaStreamDestroy(dev->stream);
@@ -183,8 +195,7 @@ int vx_mem_free(vx_buffer_h hbuffer) {
   if (nullptr == hbuffer) return 0;  // callbacks.inc:100-103
   vx_buffer* b = as_buf(hbuffer);
   cudaSetDevice(b->dev->cuda_dev);
-  cudaStreamSynchronize(b->dev->stream);  // a running kernel may still read it
-  return destroy_buffer(b);
+  return destroy_buffer(b);  // stream-ordered: work already queued on the launch stream still sees the memory
 }
 
 int vx_mem_access(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, int flags) {

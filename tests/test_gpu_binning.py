@@ -132,3 +132,62 @@ def test_errors_and_empty_inputs(d3, dev):
     with pytest.raises(vx.VortexError, match="-2"):
         t.binning(0, 8192, 8192)
     assert dev.mem_info()[1] == 0  # nothing leaked by the error paths
+
+
+# ---------------------------------------------------------------- the app flow with the pre-pass on the device
+ALL_SW = 7
+
+
+@pytest.mark.parametrize("name,size,path", od.goldens())
+def test_reference_goldens_with_gpu_binning(d3, name, size, path):
+    t = d3.Trace(blob=od.trace_blob(name))
+    with d3.Draw3D(size, size, flags=ALL_SW | d3.GPU_BINNING) as app:
+        fb = app.frame(t)
+    gold = od.golden_framebuffer(path)
+    assert np.array_equal(fb, gold), f"{(fb != gold).sum()} pixels differ from the reference golden"
+
+
+@pytest.mark.parametrize("name,w,h", [("mouse", 2048, 2048), ("vase", 4096, 4096), ("tekkaman", 1333, 777)])
+def test_large_frames_same_as_host_binned(d3, name, w, h):
+    t = d3.Trace(blob=od.trace_blob(name))
+    with d3.Draw3D(w, h, flags=ALL_SW | d3.WIDE_TILES) as app:
+        want_c, want_z = app.frame(t), app.read(depth=True)
+        st = app.stats()
+        want = (st["prims"], st["tiles"], st["tile_prims"])
+    with d3.Draw3D(w, h, flags=ALL_SW | d3.WIDE_TILES | d3.GPU_BINNING) as app:
+        got_c, got_z = app.frame(t), app.read(depth=True)
+        st = app.stats()
+        assert (st["prims"], st["tiles"], st["tile_prims"]) == want
+    assert np.array_equal(got_c, want_c) and np.array_equal(got_z, want_z)
+
+
+def test_gpu_binning_rank_strips_and_prepared_path(d3):
+    t = d3.Trace(blob=od.trace_blob("evilskull"))
+    w = h = 512
+    with d3.Draw3D(w, h, flags=ALL_SW) as app:
+        full = app.frame(t)
+    out = np.zeros_like(full)
+    for r in range(2):
+        with d3.Draw3D(w, h, flags=ALL_SW | d3.GPU_BINNING, rank=r, num_ranks=2) as app:
+            app.clear()
+            app.prepare(t)      # binned once on the device, buffers stay resident
+            app.submit()
+            app.wait()
+            part = app.read()
+        rows = [y for y in range(h) if (y // 32) % 2 == r]
+        out[rows] = part[rows]
+    assert np.array_equal(out, full)
+
+
+def test_cli_with_gpu_binning(native, tmp_path):
+    import os
+    import subprocess
+    from PIL import Image
+    exe = os.path.join(os.path.dirname(native["vortex"]), "..", "bin", "draw3d")
+    gold = np.load(os.path.join(od.GOLDEN_DIR, "box_ref_128.npy"))
+    rgba = np.stack([(gold >> 16) & 255, (gold >> 8) & 255, gold & 255, gold >> 24], -1).astype(np.uint8)
+    ref_png = str(tmp_path / "ref.png")
+    Image.fromarray(rgba, "RGBA").save(ref_png)
+    p = subprocess.run([exe, "-t", os.path.join(od.GOLDEN_DIR, "box.trc.gz"), "-w", "128", "-h", "128", "-x", "-y", "-u",
+                        "-g", "-o", str(tmp_path / "out.png"), "-r", ref_png], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0 and "PASSED!" in p.stdout, p.stdout + p.stderr
