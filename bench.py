@@ -58,7 +58,7 @@ def parse():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel, 2 wide while-while")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="N>1: weak = samples per pixel x N (per-GPU work fixed), strong = the same frame split N ways")
+                    help="N>1: weak = N x the pixels of the same view (per-GPU work fixed), strong = the same frame split N ways")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
     ap.add_argument("--keep-active", type=int, default=0, help="diagnostic: refill threshold DCR (0 = default)")
@@ -386,10 +386,14 @@ def main():
         wl["spp"] = args.spp
         wl["name"] += f" [diagnostic: spp {args.spp}]"
     if args.gpus > 1 and args.scaling == "weak" and wl["mode"] != 3:
-        # weak scaling: rows are split over the N ranks and every pixel takes N x the samples, so the
-        # rays per GPU stay those of the 1-GPU frame while the whole job grows N-fold
-        wl["spp"] = wl["spp"] * args.gpus
-        wl["name"] += f" [weak scaling: spp x {args.gpus} = {wl['spp']}]"
+        # weak scaling: the same view at sqrt(N) x the resolution in each direction, rows interleaved over the
+        # N ranks -- pixels (= jobs), samples and so rays per GPU stay those of the 1-GPU frame while the whole
+        # job grows N-fold.  The height is rounded so that every rank owns the same number of row blocks.
+        n, w0, h0 = args.gpus, wl["w"], wl["h"]
+        unit = ROWS_PER_BLOCK * n
+        wl["h"] = max(unit, int(round(h0 * n ** 0.5 / unit)) * unit)
+        wl["w"] = max(8, int(round(w0 * h0 * n / wl["h"] / 8)) * 8)
+        wl["name"] += f" [weak scaling: {n} x the pixels, {wl['w']}x{wl['h']}]"
     if args.impl == "reference":
         reference_arm(args, wl)
         return
