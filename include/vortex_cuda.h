@@ -66,6 +66,20 @@ int vx_cuda_draw3d_binning(vx_device_h hdevice, vx_buffer_h vertices, uint32_t n
                            uint32_t tile_logsize, uint32_t format, uint32_t rank, uint32_t num_ranks,
                            vx_buffer_h* tilebuf, vx_buffer_h* primbuf, srt_binning_info_t* info);
 
+/* BVH2 build on the device for the ray-tracing path: `soup` holds srt_triangle_t[num_triangles] (include/skybox_rt.h)
+ * already on the device; on success *nodes / *tris are new buffers (free with vx_mem_free) in exactly the two
+ * formats the host builder srt_build_bvh2() emits -- srt_bvh2_node_t[info->num_nodes], root = node 0, leaves of
+ * <= SRT_MAX_LEAF_TRIS triangles, and srt_tri_rec_t[num_triangles] in leaf order -- so they go straight into
+ * kernel_arg_t.node_addr / tri_addr.  A linear BVH (Morton order + radix tree), not the host's binned SAH: the
+ * tree differs, what vx_start renders from it does not (closest hit is tree-independent by construction).
+ * Some node slots are unreachable (zero).  Returns 0, or -1 on bad arguments / out of memory.  Asynchronous on the
+ * launch stream. */
+typedef struct {
+  uint32_t num_nodes, num_tris;
+} srt_lbvh_info_t;
+int vx_cuda_rt_build_lbvh(vx_device_h hdevice, vx_buffer_h soup, uint32_t num_triangles, vx_buffer_h* nodes,
+                          vx_buffer_h* tris, srt_lbvh_info_t* info);
+
 /* CUDA device ordinal the handle was opened on. */
 int vx_cuda_device(vx_device_h hdevice, int* ordinal);
 

@@ -204,7 +204,8 @@ int collapse4(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t num_tris, 
   count = 0;
   auto add_node = [&](uint32_t n) -> int {
     if (n >= num_nodes || n == 0) return -1;
-    if (n2[n].count > SRT_MAX_LEAF_TRIS || (uint64_t)n2[n].left_first + n2[n].count > num_tris) return -1;
+    // left_first is a triangle index only in a leaf; in an inner node it is a node index (checked when opened)
+    if (n2[n].count > SRT_MAX_LEAF_TRIS || (n2[n].count > 0 && (uint64_t)n2[n].left_first + n2[n].count > num_tris)) return -1;
     out[count++] = Ent{n, false, half_area(n2[n])};
     return 0;
   };
@@ -232,7 +233,7 @@ int collapse4(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t num_tris, 
     } else {
       const uint32_t l = c.left_first;
       if (l + 1 >= num_nodes || l == 0) return -1;
-      if (n2[l].count > SRT_MAX_LEAF_TRIS || (uint64_t)n2[l].left_first + n2[l].count > num_tris) return -1;
+      if (n2[l].count > SRT_MAX_LEAF_TRIS || (n2[l].count > 0 && (uint64_t)n2[l].left_first + n2[l].count > num_tris)) return -1;
       out[best] = Ent{l, false, half_area(n2[l])};
       if (add_node(l + 1)) return -1;
     }

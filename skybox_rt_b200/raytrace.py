@@ -107,23 +107,44 @@ def make_arg(width, height, mode, spp=1, seed=1234, scene="cornell", rank=0, num
 class RayTracer:
     """One opened device with one uploaded scene."""
 
-    def __init__(self, nodes, tris, device=None):
+    def __init__(self, nodes=None, tris=None, device=None, soup=None):
+        """Either the host builder's (nodes, tris) arrays, or `soup` alone: the triangle soup is uploaded and the
+        BVH is built on the device (vx_cuda_rt_build_lbvh)."""
         self.dev = device or vx.Device()
         self._own_dev = device is None
         isa = self.dev.caps(vx.VX_CAPS_ISA_FLAGS)
         if not isa & vx.VX_ISA_EXT_RT:
             raise vx.VortexError("RT extension not supported by the device")  # draw3d/main.cpp:400-417
-        nodes = np.ascontiguousarray(nodes, dtype=NODE)
-        tris = np.ascontiguousarray(tris, dtype=TRIREC)
-        self.num_nodes, self.num_tris = len(nodes), len(tris)
         self.kernel = self.dev.upload_kernel(kernel_image())
-        self.node_buf = self.dev.alloc(nodes.nbytes, vx.VX_MEM_READ)
-        self.node_buf.write(nodes)
-        self.tri_buf = self.dev.alloc(tris.nbytes, vx.VX_MEM_READ)
-        self.tri_buf.write(tris)
+        if soup is not None:
+            soup = np.ascontiguousarray(soup, dtype=TRIANGLE)
+            sbuf = self.dev.upload(soup)
+            nb, tb, info = C.c_void_p(), C.c_void_p(), (C.c_uint32 * 2)()
+            rc = vx.lib().vx_cuda_rt_build_lbvh(self.dev.handle, sbuf.handle, len(soup), C.byref(nb), C.byref(tb), info)
+            sbuf.free()
+            if rc != 0:
+                raise vx.VortexError(f"vx_cuda_rt_build_lbvh failed with code {rc}")
+            self.num_nodes, self.num_tris = info[0], info[1]
+            self.node_buf = vx.Buffer(self.dev, nb, self.num_nodes * NODE.itemsize)
+            self.tri_buf = vx.Buffer(self.dev, tb, self.num_tris * TRIREC.itemsize)
+        else:
+            nodes = np.ascontiguousarray(nodes, dtype=NODE)
+            tris = np.ascontiguousarray(tris, dtype=TRIREC)
+            self.num_nodes, self.num_tris = len(nodes), len(tris)
+            self.node_buf = self.dev.alloc(nodes.nbytes, vx.VX_MEM_READ)
+            self.node_buf.write(nodes)
+            self.tri_buf = self.dev.alloc(tris.nbytes, vx.VX_MEM_READ)
+            self.tri_buf.write(tris)
         self.cbuf = None
         self.args = None
         self.ray_buf = self.hit_buf = None
+
+    def bvh(self):
+        """The BVH2 the device holds, read back: (nodes, tris) structured arrays."""
+        nodes, tris = np.empty(self.num_nodes, NODE), np.empty(self.num_tris, TRIREC)
+        self.node_buf.read(nodes)
+        self.tri_buf.read(tris)
+        return nodes, tris
 
     def close(self):
         for b in (self.kernel, self.node_buf, self.tri_buf, self.cbuf, self.args, self.ray_buf, self.hit_buf):

@@ -40,7 +40,7 @@ EXPORTS = [
     "vx_dev_init",
 ]
 CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx_cuda_host_unregister",
-                "vx_cuda_perf_totals", "vx_cuda_draw3d_binning"]  # include/vortex_cuda.h
+                "vx_cuda_perf_totals", "vx_cuda_draw3d_binning", "vx_cuda_rt_build_lbvh"]  # include/vortex_cuda.h
 
 _lib = None
 
@@ -77,6 +77,7 @@ def lib():
             "vx_check_occupancy": [vp, u32, C.POINTER(u32)],
             "vx_cuda_stream": [vp, C.POINTER(vp)], "vx_cuda_device": [vp, C.POINTER(i)],
             "vx_cuda_perf_totals": [vp, C.POINTER(u64), u32],
+            "vx_cuda_rt_build_lbvh": [vp, vp, u32, C.POINTER(vp), C.POINTER(vp), vp],
             "vx_cuda_draw3d_binning": [vp, vp, u32, vp, u32, C.c_float, C.c_float, u32, u32, u32, u32, u32, u32,
                                        C.POINTER(vp), C.POINTER(vp), vp],
         }
