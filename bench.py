@@ -52,6 +52,8 @@ def parse():
                     help="c1..c5: the RT configs of BASELINE.json; draw3d: the raster path (bench_draw3d.py)")
     ap.add_argument("--trace", default="mouse", help="draw3d: which reference trace (tests/golden/raster/<name>.trc.gz)")
     ap.add_argument("--size", type=int, default=4096, help="draw3d: render target is size x size")
+    ap.add_argument("--builder", default="host", choices=["host", "device"],
+                    help="RT: BVH from the host binned-SAH builder (default) or built on the device (vx_cuda_rt_build_lbvh)")
     ap.add_argument("--gpu-binning", action="store_true",
                     help="draw3d: e2e leg bins on the device (vx_cuda_draw3d_binning) instead of the host pre-pass")
     ap.add_argument("--ppt", type=int, default=0, help="draw3d diagnostic: force pixels per thread (4 or 1; 0 = by grid size)")
@@ -219,7 +221,16 @@ def native_arm(args, wl):
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torch.distributed.run)"
 
     soup, nodes, tris, build_s = build_scene(wl, rt)
-    tracer = rt.RayTracer(nodes, tris)
+    device_build_ms = None
+    if args.builder == "device":
+        tracer = rt.RayTracer(soup=soup)  # warm: module load, pool growth
+        tracer.close()
+        t0 = time.perf_counter()
+        tracer = rt.RayTracer(soup=soup)
+        tracer.dev.ready_wait()
+        device_build_ms = (time.perf_counter() - t0) * 1e3  # device open + 40 MB soup upload + build
+    else:
+        tracer = rt.RayTracer(nodes, tris)
     dev = tracer.dev
     dev.dcr_write(vx.VX_DCR_RT_VARIANT, args.variant)
     dev.dcr_write(vx.VX_DCR_RT_KEEP_ACTIVE, args.keep_active)
@@ -357,7 +368,7 @@ def native_arm(args, wl):
     else:
         rays_total, kern_ms = float(rays_per_step), kern_ns * 1e-6
     return dict(rank=rank, world=world, dev_ms=dev_ms, e2e_s=e2e_s, rays_total=rays_total, kern_ms=kern_ms,
-                clocks=clocks, h2d=h2d, d2h=d2h, ctr=ctr, build_s=build_s, t_wall=t_wall, soup=soup, nodes=nodes,
+                clocks=clocks, h2d=h2d, d2h=d2h, ctr=ctr, build_s=build_s, device_build_ms=device_build_ms, t_wall=t_wall, soup=soup, nodes=nodes,
                 tris=tris, tracer=tracer, n_nodes=len(nodes), n_tris=len(tris))
 
 
@@ -440,6 +451,7 @@ def main():
                          "algorithmic_bytes": int(alg_bytes), "nodes_fetched": st["nodes"],
                          "node_bytes": int(node_bytes), "tris_tested": st["tris"]},
             "host_prepass_s": {"bvh2_build": r["build_s"]},
+            "builder": args.builder, "device_open_upload_build_ms": r.get("device_build_ms"),
         }
         if r["world"] == 1 and not args.no_cpu_baseline:
             v, sample, threads, _, _ = cpu_sample_run(wl, r["soup"], r["nodes"], r["tris"], steps=3, warmup=1)
