@@ -52,6 +52,8 @@ def parse():
                     help="c1..c5: the RT configs of BASELINE.json; draw3d: the raster path (bench_draw3d.py)")
     ap.add_argument("--trace", default="mouse", help="draw3d: which reference trace (tests/golden/raster/<name>.trc.gz)")
     ap.add_argument("--size", type=int, default=4096, help="draw3d: render target is size x size")
+    ap.add_argument("--split-samples", type=int, default=0,
+                    help="diagnostic: VX_DCR_RT_SPLIT_SAMPLES (0 = split multi-sample frames into per-sample jobs, 1 = never)")
     ap.add_argument("--builder", default="host", choices=["host", "device"],
                     help="RT: BVH from the host binned-SAH builder (default) or built on the device (vx_cuda_rt_build_lbvh)")
     ap.add_argument("--gpu-binning", action="store_true",
@@ -235,6 +237,7 @@ def native_arm(args, wl):
     dev.dcr_write(vx.VX_DCR_RT_VARIANT, args.variant)
     dev.dcr_write(vx.VX_DCR_RT_KEEP_ACTIVE, args.keep_active)
     dev.dcr_write(vx.VX_DCR_RT_PREFETCH, args.prefetch)
+    dev.dcr_write(vx.VX_DCR_RT_SPLIT_SAMPLES, args.split_samples)
     stream = torch.cuda.ExternalStream(dev.cuda_stream(), device=torch.device("cuda", local))
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.int32, device="cuda")
     launches = 0

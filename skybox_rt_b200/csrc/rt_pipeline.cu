@@ -36,9 +36,12 @@ struct RtState {
   unsigned long long* d_counters;  // CTR_COUNT u64, zeroed at every launch
   WideCache wide;
   int wide_blocks_per_sm[8];       // occupancy of the persistent kernels, queried once
+  int wide_split_blocks_per_sm[8]; // same for the (pixel, sample)-job render kernels
   int pool_blocks_per_sm[4];
   uint2* d_spill;                  // stack spill area of the pool kernels (rarely touched)
   size_t spill_warps;
+  float4* d_samples;               // per-sample radiance of split multi-sample frames, [spp][pixels]
+  size_t samples_capacity;         // in float4
 };
 
 static int rt_state(vx_device* dev, RtState** out) {
@@ -153,6 +156,7 @@ void rt_destroy(vx_device* dev) {
   cudaFree(dev->rt->d_counters);
   if (dev->rt->wide.d_nodes4) cudaFree(dev->rt->wide.d_nodes4);
   if (dev->rt->d_spill) cudaFree(dev->rt->d_spill);
+  if (dev->rt->d_samples) cudaFree(dev->rt->d_samples);
   delete dev->rt;
   dev->rt = nullptr;
 }
@@ -288,9 +292,32 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   if (rows == 0) return 0;
   const uint32_t tiles = ((a.dst_width + 7) / 8) * ((rows + 3) / 4);  // one 8x4 pixel tile = 32 jobs
   if (wide) {
-    const uint64_t jobs = (uint64_t)tiles * 32u;
+    uint64_t jobs = (uint64_t)tiles * 32u;
     if (jobs > 0xFFFFFF00ull) return -1;
-    SRT_LAUNCH_WIDE(rt_wide_render_kernel, occ, jobs, a, sc, rows, (uint32_t)jobs, st->d_counters);
+    // Multi-sample frames: one job per (pixel, sample) instead of per pixel, resolved in sample order afterwards
+    // (rt_wide.cuh).  VX_DCR_RT_SPLIT_SAMPLES: 0 = when it pays (spp > 1), 1 = never, 2 = always.
+    const uint32_t split_dcr = vx_dev_dcr(dev, VX_DCR_RT_SPLIT_SAMPLES);
+    float4* samples = nullptr;
+    const uint64_t need = (uint64_t)rows * a.dst_width * a.spp;
+    if (split_dcr != 1 && (a.spp > 1 || split_dcr == 2) && jobs * a.spp <= 0xFFFFFF00ull && need <= (4ull << 30) / sizeof(float4)) {
+      if (st->samples_capacity < need) {
+        if (st->d_samples) cudaFree(st->d_samples);
+        st->d_samples = nullptr;
+        st->samples_capacity = 0;
+        if (cudaMalloc(&st->d_samples, need * sizeof(float4)) == cudaSuccess) st->samples_capacity = need;
+        else cudaGetLastError();  // no room: per-pixel jobs, same result
+      }
+      if (st->samples_capacity >= need) {
+        samples = st->d_samples;
+        jobs *= a.spp;
+      }
+    }
+    if (samples) SRT_LAUNCH_WIDE(rt_wide_render_split_kernel, st->wide_split_blocks_per_sm + (occ - st->wide_blocks_per_sm), jobs, a, sc, rows, (uint32_t)jobs, st->d_counters, samples);
+    else SRT_LAUNCH_WIDE(rt_wide_render_kernel, occ, jobs, a, sc, rows, (uint32_t)jobs, st->d_counters, samples);
+    if (samples) {
+      rt_resolve_kernel<<<dim3((a.dst_width + 63) / 64, (rows + 3) / 4), 256, 0, s>>>(a, rows, samples);
+      ++extra_launches;
+    }
   } else {
     const uint32_t blocks = (tiles + 7) / 8;  // 8 warps per block
     if (stats) rt_baseline_kernel<true><<<blocks, 256, 0, s>>>(a, rows, st->d_counters);

@@ -92,6 +92,8 @@ struct vx_device {
 #define VX_DCR_RT_STATS   0x801 /* 1 = count node fetches / triangle tests (slower)               */
 #define VX_DCR_RT_KEEP_ACTIVE 0x802 /* tuning: refill threshold of the persistent kernels (1..32), 0 = default */
 #define VX_DCR_RT_PREFETCH 0x803 /* 1 = warm L2 with the scene before tracing when it fits (measured: no gain, off by default) */
+#define VX_DCR_RT_SPLIT_SAMPLES 0x807 /* multi-sample frames as (pixel, sample) jobs + ordered resolve: 0 = when spp > 1,
+                                        1 = never (a pixel's samples run sequentially in one lane), 2 = always */
 #define VX_DCR_RT_END     0x810
 
 inline uint32_t vx_dev_dcr(const vx_device* dev, uint32_t addr) {

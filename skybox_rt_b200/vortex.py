@@ -30,6 +30,7 @@ VX_CSR_RT_NODE_BYTES, VX_CSR_RT_LAUNCHES = 0x7C6, 0x7C7
 
 # back-end DCRs (csrc/vx_internal.h)
 VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE, VX_DCR_RT_PREFETCH = 0x800, 0x801, 0x802, 0x803
+VX_DCR_RT_SPLIT_SAMPLES = 0x807  # 0 = (pixel, sample) jobs when spp > 1, 1 = never, 2 = always
 RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL = 0, 1, 2, 3
 
 EXPORTS = [

@@ -162,3 +162,27 @@ def test_start_is_asynchronous_and_wait_times_out(terrain):
     c = tracer.counters()
     assert c["rays_primary"] == 2048 * 2048 * 4 and c["elapsed_ns"] > 0
     assert HIT.itemsize == 16
+
+
+@pytest.mark.parametrize("variant", [vx.RT_VARIANT_DEFAULT, vx.RT_VARIANT_WHILE])
+@pytest.mark.parametrize("w,h,mode,spp,ranks", [(201, 97, 2, 3, 1), (64, 64, 2, 8, 1), (130, 70, 1, 2, 3), (33, 9, 2, 1, 1)])
+def test_sample_split_jobs_render_the_same_frame(terrain, variant, w, h, mode, spp, ranks):
+    """Multi-sample frames run as (pixel, sample) jobs + an ordered resolve (VX_DCR_RT_SPLIT_SAMPLES); the
+    additions are the pixel loop's, in its order, so the frame is the one-job-per-pixel frame bit for bit."""
+    tracer, (onodes, otris), _ = terrain
+    tracer.dev.dcr_write(vx.VX_DCR_RT_VARIANT, variant)
+    try:
+        for r in range(ranks):
+            frames, counts = [], []
+            for split in (1, 0, 2):  # never / when spp > 1 / always (also for spp = 1)
+                tracer.dev.dcr_write(vx.VX_DCR_RT_SPLIT_SAMPLES, split)
+                frames.append(tracer.render(rt.make_arg(w, h, mode, spp=spp, seed=5, scene="terrain", rank=r,
+                                                        num_ranks=ranks, rows_per_block=8)))
+                counts.append(ray_counts(tracer.counters()))
+            assert np.array_equal(frames[0], frames[1]) and np.array_equal(frames[0], frames[2])
+            assert counts[0] == counts[1] == counts[2]
+        if ranks == 1:
+            ref, _ = o.render(o.make_arg(w, h, mode, spp=spp, seed=5, scene="terrain"), onodes, otris)
+            assert np.array_equal(frames[0], ref)
+    finally:
+        tracer.dev.dcr_write(vx.VX_DCR_RT_SPLIT_SAMPLES, 0)
