@@ -80,6 +80,10 @@ typedef struct {
 int vx_cuda_rt_build_lbvh(vx_device_h hdevice, vx_buffer_h soup, uint32_t num_triangles, vx_buffer_h* nodes,
                           vx_buffer_h* tris, srt_lbvh_info_t* info);
 
+/* The wide-BVH image (128-byte SoA Node4 records, csrc/rt_repack.h) the last ray-tracing vx_start traversed, for
+ * tests and tooling: *size = its size in bytes; copied to dst when dst != NULL and capacity suffices. */
+int vx_cuda_rt_node4_image(vx_device_h hdevice, void* dst, uint64_t capacity, uint64_t* size);
+
 /* CUDA device ordinal the handle was opened on. */
 int vx_cuda_device(vx_device_h hdevice, int* ordinal);
 

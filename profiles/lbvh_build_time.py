@@ -42,5 +42,33 @@ def main():
             print(f"{len(soup):>10} {host_s:>11.2f} {best:>10.3f} {len(soup) / best / 1e3:>8.0f}")
 
 
+def first_frame():
+    """Scene change to first pixels: build + BVH2 -> Node4 repack + one 64x64 frame, wall clock."""
+    print()
+    print(f"{'triangles':>10} {'builder':>8} {'repack':>7} {'build ms':>9} {'first frame ms (incl. repack)':>30}")
+    for qx, qy in ((1000, 500), (2500, 2000)):
+        soup = rt.scene_terrain(qx, qy)
+        for builder in ("host", "device"):
+            if builder == "host" and len(soup) > 1000000:
+                continue
+            for repack in (1, 0):
+                for it in range(2):  # second pass: pools and modules warm
+                    t0 = time.perf_counter()
+                    if builder == "host":
+                        nodes, tris = rt.build_bvh2(soup)
+                        t = rt.RayTracer(nodes, tris)
+                    else:
+                        t = rt.RayTracer(soup=soup)
+                    t.dev.ready_wait()
+                    build_ms = (time.perf_counter() - t0) * 1e3
+                    t.dev.dcr_write(vx.VX_DCR_RT_REPACK, repack)
+                    t0 = time.perf_counter()
+                    t.render(rt.make_arg(64, 64, 0, scene="terrain"))
+                    frame_ms = (time.perf_counter() - t0) * 1e3
+                    t.close()
+                print(f"{len(soup):>10} {builder:>8} {'host' if repack else 'device':>7} {build_ms:>9.1f} {frame_ms:>30.2f}")
+
+
 if __name__ == "__main__":
     main()
+    first_frame()

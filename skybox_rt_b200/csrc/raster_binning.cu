@@ -25,6 +25,7 @@
 #include <string.h>
 
 #include "raster_tile.cuh"
+#include "scan.cuh"
 #include "vx_internal.h"
 
 namespace srt {
@@ -152,91 +153,6 @@ __device__ __forceinline__ bool setup_one(const BinParams& P, uint32_t n, int32_
   if (ty0 > ty1) ty0 = ty1;
   *rect = TileRect{(uint16_t)tx0, (uint16_t)tx1, (uint16_t)ty0, (uint16_t)ty1};
   return true;
-}
-
-// ---- exclusive scan of (v, v != 0) over a u32 array: reduce / spine / apply ---------------------------
-constexpr int kScanThreads = 256, kScanPerThread = 8, kScanTile = kScanThreads * kScanPerThread;
-
-__device__ __forceinline__ uint2 add2(uint2 a, uint2 b) { return make_uint2(a.x + b.x, a.y + b.y); }
-
-// CTA-wide exclusive scan of one uint2 per thread; returns the exclusive prefix, *total = CTA sum
-__device__ __forceinline__ uint2 cta_exclusive(uint2 v, uint2* total) {
-  __shared__ uint2 s_warp[kScanThreads / 32];
-  __shared__ uint2 s_total;
-  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint2 inc = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t ax = __shfl_up_sync(0xffffffffu, inc.x, o), ay = __shfl_up_sync(0xffffffffu, inc.y, o);
-    if (lane >= (uint32_t)o) { inc.x += ax; inc.y += ay; }
-  }
-  __syncthreads();  // s_warp may still be read from the previous call
-  if (lane == 31) s_warp[warp] = inc;
-  __syncthreads();
-  if (warp == 0) {
-    uint2 w = lane < kScanThreads / 32 ? s_warp[lane] : make_uint2(0, 0);
-    uint2 winc = w;
-#pragma unroll
-    for (int o = 1; o < kScanThreads / 32; o <<= 1) {
-      const uint32_t ax = __shfl_up_sync(0xffffffffu, winc.x, o), ay = __shfl_up_sync(0xffffffffu, winc.y, o);
-      if (lane >= (uint32_t)o) { winc.x += ax; winc.y += ay; }
-    }
-    if (lane < kScanThreads / 32) s_warp[lane] = make_uint2(winc.x - w.x, winc.y - w.y);
-    if (lane == kScanThreads / 32 - 1) s_total = winc;
-  }
-  __syncthreads();
-  const uint2 base = s_warp[warp];
-  *total = s_total;
-  return make_uint2(base.x + inc.x - v.x, base.y + inc.y - v.y);
-}
-
-__global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(const uint32_t* __restrict__ in, uint32_t n,
-                                                                    uint2* __restrict__ block_sums) {
-  const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanPerThread;
-  uint2 s = make_uint2(0, 0);
-#pragma unroll
-  for (int k = 0; k < kScanPerThread; ++k) {
-    const uint32_t v = base + k < n ? in[base + k] : 0u;
-    s.x += v; s.y += v != 0u;
-  }
-  uint2 total;
-  cta_exclusive(s, &total);
-  if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
-}
-
-// one CTA: block_sums -> exclusive prefixes in place, grand total to totals[0]
-__global__ void __launch_bounds__(kScanThreads) scan_spine_kernel(uint2* __restrict__ block_sums, uint32_t num_blocks,
-                                                                   uint2* __restrict__ totals) {
-  uint2 carry = make_uint2(0, 0);
-  for (uint32_t base = 0; base < num_blocks; base += kScanThreads) {
-    const uint32_t i = base + threadIdx.x;
-    const uint2 v = i < num_blocks ? block_sums[i] : make_uint2(0, 0);
-    uint2 total;
-    const uint2 ex = cta_exclusive(v, &total);
-    if (i < num_blocks) block_sums[i] = add2(carry, ex);
-    carry = add2(carry, total);
-  }
-  if (threadIdx.x == 0) totals[0] = carry;
-}
-
-__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint32_t* __restrict__ in, uint32_t n,
-                                                                   const uint2* __restrict__ block_sums,
-                                                                   uint2* __restrict__ out) {
-  const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanPerThread;
-  uint32_t v[kScanPerThread];
-  uint2 s = make_uint2(0, 0);
-#pragma unroll
-  for (int k = 0; k < kScanPerThread; ++k) {
-    v[k] = base + k < n ? in[base + k] : 0u;
-    s.x += v[k]; s.y += v[k] != 0u;
-  }
-  uint2 total;
-  uint2 run = add2(block_sums[blockIdx.x], cta_exclusive(s, &total));
-#pragma unroll
-  for (int k = 0; k < kScanPerThread; ++k) {
-    if (base + k < n) out[base + k] = run;
-    run.x += v[k]; run.y += v[k] != 0u;
-  }
 }
 
 // ---- count / fill: one lane per submitted triangle; a triangle touching many tiles is shared by its warp ----
@@ -375,15 +291,6 @@ __global__ void __launch_bounds__(256) bin_sort_kernel(const uint32_t* __restric
   } else {
     bitonic_ascending((volatile uint32_t*)list, n);  // in place; __syncthreads orders the CTA's global accesses
   }
-}
-
-int scan_u32(cudaStream_t s, const uint32_t* in, uint32_t n, uint2* block_sums, uint2* out, uint2* totals) {
-  const uint32_t blocks = (n + kScanTile - 1) / kScanTile;
-  scan_reduce_kernel<<<blocks, kScanThreads, 0, s>>>(in, n, block_sums);
-  scan_spine_kernel<<<1, kScanThreads, 0, s>>>(block_sums, blocks, totals);
-  scan_apply_kernel<<<blocks, kScanThreads, 0, s>>>(in, n, block_sums, out);
-  VX_CUDA_OK(cudaGetLastError());
-  return 0;
 }
 
 // One stream-ordered allocation per call, carved into 256-byte aligned pieces; the pieces that must start at zero

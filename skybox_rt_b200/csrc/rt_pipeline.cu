@@ -77,36 +77,47 @@ static int wide_prepare(vx_device* dev, RtState* st, const kernel_arg_t& a) {
   if (c.valid && c.node_addr == a.node_addr && c.tri_addr == a.tri_addr && c.num_nodes == a.num_nodes &&
       c.num_tris == a.num_tris && c.generation == nb->generation + tb->generation)
     return 0;
-  // read the builder's BVH2 back (the app uploaded it; the back-end keeps no host copy of large
-  // buffers) and repack it on the host: once per scene, not part of a frame
-  std::vector<srt_bvh2_node_t> n2(a.num_nodes);
-  VX_CUDA_OK(cudaMemcpyAsync(n2.data(), (const char*)nb->dptr + (a.node_addr - nb->reported_addr),
-                             n2.size() * sizeof(srt_bvh2_node_t), cudaMemcpyDeviceToHost, dev->stream));
-  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
-  std::vector<srt_tri_rec_t> tr(a.num_tris);
-  VX_CUDA_OK(cudaMemcpyAsync(tr.data(), (const char*)tb->dptr + (a.tri_addr - tb->reported_addr),
-                             tr.size() * sizeof(srt_tri_rec_t), cudaMemcpyDeviceToHost, dev->stream));
-  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
-  std::vector<Node4> n4;
-  uint32_t depth = 0;
-  if (repack_bvh4(n2.data(), a.num_nodes, tr.data(), a.num_tris, n4, &depth) != 0) {
+  const srt_bvh2_node_t* d_n2 = reinterpret_cast<const srt_bvh2_node_t*>((const char*)nb->dptr + (a.node_addr - nb->reported_addr));
+  const srt_tri_rec_t* d_tr = reinterpret_cast<const srt_tri_rec_t*>((const char*)tb->dptr + (a.tri_addr - tb->reported_addr));
+  float4* d_n4 = nullptr;
+  uint32_t depth = 0, count4 = 0;
+  if (vx_dev_dcr(dev, VX_DCR_RT_REPACK) == 1) {
+    // A/B path: read the builder's BVH2 back and repack it on the host (rt_repack.cpp) -- the same bytes
+    std::vector<srt_bvh2_node_t> n2(a.num_nodes);
+    VX_CUDA_OK(cudaMemcpyAsync(n2.data(), d_n2, n2.size() * sizeof(srt_bvh2_node_t), cudaMemcpyDeviceToHost, dev->stream));
+    std::vector<srt_tri_rec_t> tr(a.num_tris);
+    VX_CUDA_OK(cudaMemcpyAsync(tr.data(), d_tr, tr.size() * sizeof(srt_tri_rec_t), cudaMemcpyDeviceToHost, dev->stream));
+    VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+    std::vector<Node4> n4;
+    if (repack_bvh4(n2.data(), a.num_nodes, tr.data(), a.num_tris, n4, &depth) != 0) {
+      fprintf(stderr, "[VXDRV] raytrace: malformed BVH2 (child / triangle range out of bounds, or a leaf with more "
+                      "than %d triangles)\n", SRT_MAX_LEAF_TRIS);
+      return -1;
+    }
+    count4 = (uint32_t)n4.size();
+    VX_CUDA_OK(cudaMalloc(&d_n4, n4.size() * sizeof(Node4)));
+    VX_CUDA_OK(cudaMemcpyAsync(d_n4, n4.data(), n4.size() * sizeof(Node4), cudaMemcpyHostToDevice, dev->stream));
+    VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  } else if (repack_bvh4_device(dev->stream, d_n2, a.num_nodes, d_tr, a.num_tris, &d_n4, &count4, &depth) != 0) {
+    // the repack where the data is: once per scene, level by level (rt_repack_device.cu)
     fprintf(stderr, "[VXDRV] raytrace: malformed BVH2 (child / triangle range out of bounds, or a leaf with more "
                     "than %d triangles)\n", SRT_MAX_LEAF_TRIS);
     return -1;
   }
   if (3u * depth + 1u > (uint32_t)(kSmStack + kLocalStack)) {
     fprintf(stderr, "[VXDRV] raytrace: BVH too deep for the traversal stack (%u wide levels)\n", depth);
+    cudaFree(d_n4);
     return -1;
   }
-  if (c.d_nodes4) cudaFree(c.d_nodes4);
-  c.d_nodes4 = nullptr;
+  if (c.d_nodes4) {
+    VX_CUDA_OK(cudaStreamSynchronize(dev->stream));  // a queued frame may still read the previous image
+    cudaFree(c.d_nodes4);
+  }
+  c.d_nodes4 = d_n4;
   c.valid = false;
-  VX_CUDA_OK(cudaMalloc(&c.d_nodes4, n4.size() * sizeof(Node4)));
-  VX_CUDA_OK(cudaMemcpyAsync(c.d_nodes4, n4.data(), n4.size() * sizeof(Node4), cudaMemcpyHostToDevice, dev->stream));
-  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
   c.node_addr = a.node_addr; c.tri_addr = a.tri_addr; c.generation = nb->generation + tb->generation;
   c.num_nodes = a.num_nodes; c.num_tris = a.num_tris;
-  c.num_nodes4 = (uint32_t)n4.size(); c.depth = depth;
+  c.num_nodes4 = count4; c.depth = depth;
   c.valid = true;
   return 0;
 }
@@ -341,3 +352,18 @@ int rt_read_counters(vx_device* dev) {
 }
 
 }  // namespace srt
+
+// Test / tooling hook (include/vortex_cuda.h): the Node4 image the last ray-tracing vx_start traversed.
+extern "C" int vx_cuda_rt_node4_image(vx_device_h hdevice, void* dst, uint64_t capacity, uint64_t* size) {
+  if (nullptr == hdevice || nullptr == size) return -1;
+  vx_device* dev = static_cast<vx_device*>(hdevice);
+  if (!dev->rt || !dev->rt->wide.valid) return -1;
+  const srt::WideCache& c = dev->rt->wide;
+  *size = (uint64_t)c.num_nodes4 * sizeof(srt::Node4);
+  if (nullptr == dst) return 0;
+  if (capacity < *size) return -1;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaMemcpyAsync(dst, c.d_nodes4, *size, cudaMemcpyDeviceToHost, dev->stream));
+  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  return 0;
+}

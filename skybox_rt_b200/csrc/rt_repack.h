@@ -1,6 +1,7 @@
 // rt_repack.h -- device layout of the wide BVH and the host repack entry point (rt_repack.cpp).
 #pragma once
 
+#include <cuda_runtime.h>
 #include <stdint.h>
 
 #include <vector>
@@ -45,6 +46,12 @@ float scene_delta_host(const srt_bvh2_node_t& root);
 // (child / triangle range out of bounds, leaf larger than SRT_MAX_LEAF_TRIS, cycle).
 int repack_bvh4(const srt_bvh2_node_t* nodes2, uint32_t num_nodes, const srt_tri_rec_t* tris, uint32_t num_tris,
                 std::vector<Node4>& out_nodes, uint32_t* max_depth);
+
+// The same on the device (rt_repack_device.cu): d_nodes2 / d_tris are device pointers, *d_out is cudaMalloc'ed and
+// owned by the caller.  Byte-identical to repack_bvh4's output.
+int repack_bvh4_device(cudaStream_t stream, const srt_bvh2_node_t* d_nodes2, uint32_t num_nodes,
+                       const srt_tri_rec_t* d_tris, uint32_t num_tris, float4** d_out, uint32_t* num_nodes4,
+                       uint32_t* max_depth);
 
 // Returns 0 on success.  out_tris is a permutation of tris.
 int repack_bvh8(const srt_bvh2_node_t* nodes2, uint32_t num_nodes, const srt_tri_rec_t* tris, uint32_t num_tris,

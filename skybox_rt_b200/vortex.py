@@ -30,6 +30,7 @@ VX_CSR_RT_NODE_BYTES, VX_CSR_RT_LAUNCHES = 0x7C6, 0x7C7
 
 # back-end DCRs (csrc/vx_internal.h)
 VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE, VX_DCR_RT_PREFETCH = 0x800, 0x801, 0x802, 0x803
+VX_DCR_RT_REPACK = 0x808  # 0 = BVH2 -> Node4 on the device, 1 = on the host (A/B)
 VX_DCR_RT_SPLIT_SAMPLES = 0x807  # 0 = (pixel, sample) jobs when spp > 1, 1 = never, 2 = always
 RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL = 0, 1, 2, 3
 
@@ -41,7 +42,8 @@ EXPORTS = [
     "vx_dev_init",
 ]
 CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx_cuda_host_unregister",
-                "vx_cuda_perf_totals", "vx_cuda_draw3d_binning", "vx_cuda_rt_build_lbvh"]  # include/vortex_cuda.h
+                "vx_cuda_perf_totals", "vx_cuda_draw3d_binning", "vx_cuda_rt_build_lbvh",
+                "vx_cuda_rt_node4_image"]  # include/vortex_cuda.h
 
 _lib = None
 
@@ -79,6 +81,7 @@ def lib():
             "vx_cuda_stream": [vp, C.POINTER(vp)], "vx_cuda_device": [vp, C.POINTER(i)],
             "vx_cuda_perf_totals": [vp, C.POINTER(u64), u32],
             "vx_cuda_rt_build_lbvh": [vp, vp, u32, C.POINTER(vp), C.POINTER(vp), vp],
+            "vx_cuda_rt_node4_image": [vp, vp, u64, C.POINTER(u64)],
             "vx_cuda_draw3d_binning": [vp, vp, u32, vp, u32, C.c_float, C.c_float, u32, u32, u32, u32, u32, u32,
                                        C.POINTER(vp), C.POINTER(vp), vp],
         }
@@ -193,6 +196,14 @@ class Device:
         v = C.c_uint64()
         _check(lib().vx_mpm_query(self.handle, addr, core_id, C.byref(v)), "vx_mpm_query")
         return v.value
+
+    def node4_image(self):
+        """Bytes of the Node4 image the last ray-tracing run traversed (vx_cuda_rt_node4_image)."""
+        n = C.c_uint64()
+        _check(lib().vx_cuda_rt_node4_image(self.handle, None, 0, C.byref(n)), "vx_cuda_rt_node4_image")
+        out = np.zeros(n.value, np.uint8)
+        _check(lib().vx_cuda_rt_node4_image(self.handle, out.ctypes.data, n.value, C.byref(n)), "vx_cuda_rt_node4_image")
+        return out.tobytes()
 
     def perf_totals(self):
         """Accumulated performance-monitor totals, slots VX_PERF_* of include/vortex_cuda.h."""

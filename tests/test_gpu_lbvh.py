@@ -164,3 +164,49 @@ def test_errors(native):
         assert L.vx_cuda_rt_build_lbvh(dev.handle, None, 1, C.byref(nb), C.byref(tb), info) == -1
         buf.free()
         assert dev.mem_info()[1] == 0
+
+
+# ---------------------------------------------------------------- BVH2 -> Node4 repack on the device
+def _node4_images(make_tracer, w=48, h=32):
+    out = []
+    for mode in (1, 0):  # host repack (rt_repack.cpp), device repack (rt_repack_device.cu)
+        with make_tracer() as t:
+            t.dev.dcr_write(vx.VX_DCR_RT_REPACK, mode)
+            fb = t.render(rt.make_arg(w, h, 2, spp=1, seed=3, scene="terrain"))
+            out.append((t.dev.node4_image(), fb))
+    return out
+
+
+@pytest.mark.parametrize("builder", ["sah", "lbvh"])
+@pytest.mark.parametrize("quads", [(1, 1), (3, 2), (40, 30), (250, 200)])
+def test_device_repack_equals_host_repack(native, builder, quads):
+    """The Node4 image built level by level on the device is the host routine's, byte for byte."""
+    soup = rt.scene_terrain(*quads)
+    if builder == "sah":
+        nodes, tris = rt.build_bvh2(soup)
+        make = lambda: rt.RayTracer(nodes, tris)
+    else:
+        make = lambda: rt.RayTracer(soup=soup)
+    (host_img, host_fb), (dev_img, dev_fb) = _node4_images(make)
+    assert len(host_img) == len(dev_img) and len(host_img) % 128 == 0 and len(host_img) > 0
+    assert host_img == dev_img, f"{sum(a != b for a, b in zip(host_img, dev_img))} bytes differ"
+    assert np.array_equal(host_fb, dev_fb)
+
+
+def test_device_repack_refuses_what_the_host_repack_refuses(native):
+    soup = rt.scene_terrain(20, 20)
+    nodes, tris = rt.build_bvh2(soup)
+    bad = []
+    n = nodes.copy(); n["left_first"][0] = len(nodes) + 5; bad.append(n)          # child out of range
+    n = nodes.copy(); n["left_first"][0] = 0; bad.append(n)                        # the root as its own child
+    leaf = int(np.nonzero(nodes["count"] > 0)[0][0])
+    n = nodes.copy(); n["count"][leaf] = 5; bad.append(n)                          # leaf larger than SRT_MAX_LEAF_TRIS
+    n = nodes.copy(); n["left_first"][leaf] = len(tris); bad.append(n)             # triangle range out of bounds
+    inner = int(np.nonzero(nodes["count"] == 0)[0][3])
+    n = nodes.copy(); n["left_first"][inner] = 1; bad.append(n)                    # a cycle
+    for mode in (0, 1):
+        for k, n in enumerate(bad):
+            with rt.RayTracer(n, tris) as t:
+                t.dev.dcr_write(vx.VX_DCR_RT_REPACK, mode)
+                with pytest.raises(vx.VortexError):
+                    t.render(rt.make_arg(16, 16, 0))
