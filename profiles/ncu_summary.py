@@ -1,5 +1,6 @@
 """Summarise an .ncu-rep into the handful of counters DESIGN.md argues from.
-usage: python profiles/ncu_summary.py gpurun_out/x.ncu-rep > profiles/x_summary.txt"""
+usage: python profiles/ncu_summary.py gpurun_out/x.ncu-rep [--last] > profiles/x_summary.txt
+--last: only the last launch of every distinct kernel (a capture of several identical calls)."""
 import csv
 import subprocess
 import sys
@@ -29,11 +30,17 @@ WANT = [
 ]
 
 
-def main(path):
+def main(path, last=False):
     raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     head, units = rows[0], rows[1]
-    for r in rows[2:]:
+    body = rows[2:]
+    if last:
+        keep = {}
+        for n, r in enumerate(body):
+            keep[r[head.index("Kernel Name")]] = n
+        body = [r for n, r in enumerate(body) if keep[r[head.index("Kernel Name")]] == n]
+    for r in body:
         print("==", r[head.index("Kernel Name")], "grid", r[head.index("Grid Size")], "block", r[head.index("Block Size")])
         for w in WANT:
             if w in head:
@@ -42,4 +49,4 @@ def main(path):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1])
+    main(sys.argv[1], "--last" in sys.argv[2:])

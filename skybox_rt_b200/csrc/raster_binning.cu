@@ -57,40 +57,41 @@ __device__ __forceinline__ V4 to_screen(V4 c, const BinParams& P) {  // math.hpp
   const float rhw = (c.w != 0.0f) ? (1.0f / c.w) : 0.0f;
   return V4{(c.x * rhw) * P.scale_x + P.min_x, (c.y * rhw) * P.scale_y + P.min_y, (c.z * rhw) * P.scale_z + P.min_z, rhw};
 }
-template <class Rec>
-__device__ __forceinline__ void plane(Rec rec, int w, uint32_t t, float a0, float a1, float a2) {  // ATTRIBUTE_DELTA, gfxutil.cpp:189-192
-  rec[w + 0][t] = to_fixed(a0 - a2, 16777216.0f);
-  rec[w + 1][t] = to_fixed(a1 - a2, 16777216.0f);
-  rec[w + 2][t] = to_fixed(a2, 16777216.0f);
+__device__ __forceinline__ void plane(int32_t* d, float a0, float a1, float a2) {  // ATTRIBUTE_DELTA, gfxutil.cpp:189-192
+  d[0] = to_fixed(a0 - a2, 16777216.0f);
+  d[1] = to_fixed(a1 - a2, 16777216.0f);
+  d[2] = to_fixed(a2, 16777216.0f);
 }
 
 // ---- setup: one thread per submitted triangle -------------------------------------------------------
-// Each thread builds its record in shared memory ([word][thread]: conflict-free); the CTA then writes its 128
-// records to tmp_prims as one contiguous, coalesced block.
-constexpr int kSetupThreads = 128;
+// Each thread builds its record in shared memory (row = thread, 30 words padded to 31: conflict-free for the
+// per-thread stores and for the linear read-out); the CTA then writes its 128 records to tmp_prims as one
+// contiguous, coalesced block.
+constexpr int kSetupThreads = 128, kRecPitch = 31;
 
-__device__ __forceinline__ bool setup_one(const BinParams& P, uint32_t n, int32_t (*rec)[kSetupThreads], TileRect* rect,
-                                          uint32_t* error);
+__device__ __forceinline__ bool setup_one(const BinParams& P, uint32_t n, int32_t* rec, TileRect* rect, uint32_t* error);
 
 __global__ void __launch_bounds__(kSetupThreads) bin_setup_kernel(const BinParams P, int32_t* __restrict__ tmp_prims,
                                                                   TileRect* __restrict__ rects, uint32_t* __restrict__ keep,
                                                                   uint32_t* __restrict__ error) {
-  __shared__ int32_t s_rec[30][kSetupThreads];
+  __shared__ int32_t s_rec[kSetupThreads * kRecPitch];
   const uint32_t first = blockIdx.x * kSetupThreads, n = first + threadIdx.x;
   if (n < P.num_primitives) {
     TileRect r = {0, 0, 0, 0};
-    const bool k = setup_one(P, n, s_rec, &r, error);
+    const bool k = setup_one(P, n, s_rec + threadIdx.x * kRecPitch, &r, error);
     keep[n] = k ? 1u : 0u;
     rects[n] = r;
   }
   __syncthreads();
   const uint32_t in_cta = min((uint32_t)kSetupThreads, P.num_primitives - first);
   int32_t* dst = tmp_prims + (size_t)first * 30;
-  for (uint32_t w = threadIdx.x; w < in_cta * 30; w += kSetupThreads) dst[w] = s_rec[w % 30][w / 30];
+  for (uint32_t w = threadIdx.x; w < in_cta * 30; w += kSetupThreads) {
+    const uint32_t t = w / 30u;
+    dst[w] = s_rec[t * kRecPitch + (w - t * 30u)];
+  }
 }
 
-__device__ __forceinline__ bool setup_one(const BinParams& P, uint32_t n, int32_t (*rec)[kSetupThreads], TileRect* rect,
-                                          uint32_t* error) {
+__device__ __forceinline__ bool setup_one(const BinParams& P, uint32_t n, int32_t* rec, TileRect* rect, uint32_t* error) {
   const srt_primitive_t tri = P.primitives[n];
   if (tri.i0 >= P.num_vertices || tri.i1 >= P.num_vertices || tri.i2 >= P.num_vertices) {
     atomicOr(error, 1u);  // the host loader refuses such a trace; never read out of bounds
@@ -130,18 +131,17 @@ __device__ __forceinline__ bool setup_one(const BinParams& P, uint32_t n, int32_
   m = max_f(m, fabsf(e[1][0])); m = max_f(m, fabsf(e[2][0]));
   m = max_f(m, fabsf(e[0][1])); m = max_f(m, fabsf(e[1][1])); m = max_f(m, fabsf(e[2][1]));
   const float scale = 1.0f / m;
-  const uint32_t t_ = threadIdx.x;
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
-    rec[3 * i + 0][t_] = to_fixed(e[i][0] * scale, 65536.0f);
-    rec[3 * i + 1][t_] = to_fixed(e[i][1] * scale, 65536.0f);
-    rec[3 * i + 2][t_] = to_fixed(e[i][2] * scale, 65536.0f);
+    rec[3 * i + 0] = to_fixed(e[i][0] * scale, 65536.0f);
+    rec[3 * i + 1] = to_fixed(e[i][1] * scale, 65536.0f);
+    rec[3 * i + 2] = to_fixed(e[i][2] * scale, 65536.0f);
   }
-  plane(rec, 9, t_, s0.z, s1.z, s2.z);
+  plane(rec + 9, s0.z, s1.z, s2.z);
 #pragma unroll
-  for (int k = 0; k < 4; ++k) plane(rec, 12 + 3 * k, t_, v0->color[k], v1->color[k], v2->color[k]);
-  plane(rec, 24, t_, v0->texcoord[0], v1->texcoord[0], v2->texcoord[0]);
-  plane(rec, 27, t_, v0->texcoord[1], v1->texcoord[1], v2->texcoord[1]);
+  for (int k = 0; k < 4; ++k) plane(rec + 12 + 3 * k, v0->color[k], v1->color[k], v2->color[k]);
+  plane(rec + 24, v0->texcoord[0], v1->texcoord[0], v2->texcoord[0]);
+  plane(rec + 27, v0->texcoord[1], v1->texcoord[1], v2->texcoord[1]);
   // tiles touched (gfxutil.cpp:221-235), clamped to the grid exactly as the host pre-pass does
   const uint32_t tile = 1u << P.L;
   uint32_t tx0 = left >> P.L, tx1 = (right + tile - 1) >> P.L, ty0 = top >> P.L, ty1 = (bottom + tile - 1) >> P.L;
@@ -200,14 +200,30 @@ __global__ void __launch_bounds__(256) bin_count_kernel(const BinParams P, const
   if ((threadIdx.x & 31) == 0 && mine) atomicAdd(pairs, (unsigned long long)mine);  // 64-bit total: the u32 scan may wrap
 }
 
-// ---- compact: kept records -> primbuf[pid], one thread per 8-byte word (coalesced both ways) ---------------
+// ---- compact: kept records -> primbuf[pid]; 8-byte words, four per thread in flight (coalesced both ways) ----
+constexpr uint32_t kCompactPerThread = 4;
+
 __global__ void __launch_bounds__(256) bin_compact_kernel(const uint2* __restrict__ tmp_prims, const uint32_t* __restrict__ keep,
                                                           const uint2* __restrict__ pid_of, uint32_t num_words,
                                                           uint2* __restrict__ primbuf) {
-  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;  // 15 words per 120-byte record
-  if (w >= num_words) return;
-  const uint32_t n = w / 15u, j = w - n * 15u;
-  if (keep[n]) primbuf[(size_t)pid_of[n].x * 15 + j] = tmp_prims[w];
+  const uint32_t base = blockIdx.x * (256u * kCompactPerThread) + threadIdx.x;  // 15 words per 120-byte record
+  uint2 v[kCompactPerThread];
+  uint32_t dst[kCompactPerThread];
+#pragma unroll
+  for (uint32_t k = 0; k < kCompactPerThread; ++k) {
+    const uint32_t w = base + k * 256u;
+    dst[k] = 0xffffffffu;
+    if (w < num_words) {
+      const uint32_t n = w / 15u;
+      if (keep[n]) {
+        dst[k] = pid_of[n].x * 15u + (w - n * 15u);  // < 2^27 * 15
+        v[k] = __ldcs(tmp_prims + w);
+      }
+    }
+  }
+#pragma unroll
+  for (uint32_t k = 0; k < kCompactPerThread; ++k)
+    if (dst[k] != 0xffffffffu) primbuf[dst[k]] = v[k];
 }
 
 // ---- headers: one thread per grid cell, x-major like std::map<pair<tile_x, tile_y>> (gfxutil.cpp:243-262)
@@ -257,7 +273,8 @@ __device__ __forceinline__ void bitonic_ascending(Ptr a, uint32_t n) {
   for (uint32_t size = 2; size <= pow2; size <<= 1) {
     const uint32_t half = size >> 1;
     for (uint32_t t = threadIdx.x; t < pow2 / 2; t += blockDim.x) {
-      const uint32_t grp = t / half, off = t % half, i = grp * size + off, j = grp * size + size - 1 - off;
+      // half and stride are powers of two: masks and shifts, no division
+      const uint32_t off = t & (half - 1), base = (t & ~(half - 1)) << 1, i = base + off, j = base + size - 1 - off;
       if (j < n) {
         const uint32_t x = a[i], y = a[j];
         if (x > y) { a[i] = y; a[j] = x; }
@@ -266,7 +283,7 @@ __device__ __forceinline__ void bitonic_ascending(Ptr a, uint32_t n) {
     __syncthreads();
     for (uint32_t stride = half >> 1; stride > 0; stride >>= 1) {
       for (uint32_t t = threadIdx.x; t < pow2 / 2; t += blockDim.x) {
-        const uint32_t i = 2 * stride * (t / stride) + t % stride, j = i + stride;
+        const uint32_t i = ((t & ~(stride - 1)) << 1) + (t & (stride - 1)), j = i + stride;
         if (j < n) {
           const uint32_t x = a[i], y = a[j];
           if (x > y) { a[i] = y; a[j] = x; }
@@ -283,6 +300,11 @@ __global__ void __launch_bounds__(256) bin_sort_kernel(const uint32_t* __restric
   const uint32_t g = blockIdx.x, n = count[g];
   if (n < 2) return;
   uint32_t* list = pids + cursor[g].x;
+  {  // arrival order is often already submission order: one pass to find out
+    int unsorted = 0;
+    for (uint32_t i = threadIdx.x + 1; i < n; i += blockDim.x) unsorted |= list[i - 1] > list[i];
+    if (!__syncthreads_or(unsorted)) return;
+  }
   if (n <= kSortShared) {
     for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_list[i] = list[i];
     __syncthreads();
@@ -408,7 +430,7 @@ extern "C" int vx_cuda_draw3d_binning(vx_device_h hdevice, vx_buffer_h hvertices
   if (num_prims) {
     if (vx_mem_alloc(hdevice, info->primbuf_size, VX_MEM_READ, &prb) != 0) return -1;
     const uint32_t words = np * 15u;  // np <= 2^27
-    bin_compact_kernel<<<(words + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(tmp_prims), keep, pid_of, words,
+    bin_compact_kernel<<<(words + 256 * kCompactPerThread - 1) / (256 * kCompactPerThread), 256, 0, s>>>(reinterpret_cast<const uint2*>(tmp_prims), keep, pid_of, words,
                                                            static_cast<uint2*>(static_cast<vx_buffer*>(prb)->dptr));
   }
   if (num_tiles) {

@@ -111,7 +111,7 @@ __device__ __forceinline__ void cmpx(unsigned long long& a, unsigned long long& 
 __device__ __forceinline__ void local_halves(unsigned long long* s, uint32_t from) {
   for (uint32_t stride = from; stride > 0; stride >>= 1) {
     for (uint32_t t = threadIdx.x; t < kChunk / 2; t += blockDim.x) {
-      const uint32_t i = 2 * stride * (t / stride) + t % stride;
+      const uint32_t i = ((t & ~(stride - 1)) << 1) + (t & (stride - 1));  // stride is a power of two
       cmpx(s[i], s[i + stride]);
     }
     __syncthreads();
@@ -126,8 +126,8 @@ __global__ void __launch_bounds__(512) sort_local_kernel(unsigned long long* __r
   for (uint32_t size = 2; size <= kChunk; size <<= 1) {
     const uint32_t half = size >> 1;
     for (uint32_t t = threadIdx.x; t < kChunk / 2; t += blockDim.x) {
-      const uint32_t grp = t / half, off = t % half;
-      cmpx(s[grp * size + off], s[grp * size + size - 1 - off]);
+      const uint32_t off = t & (half - 1), base = (t & ~(half - 1)) << 1;
+      cmpx(s[base + off], s[base + size - 1 - off]);
     }
     __syncthreads();
     local_halves(s, half >> 1);
@@ -138,8 +138,8 @@ __global__ void __launch_bounds__(512) sort_local_kernel(unsigned long long* __r
 __global__ void __launch_bounds__(256) sort_flip_kernel(unsigned long long* __restrict__ keys, uint32_t size, uint32_t pairs) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= pairs) return;
-  const uint32_t half = size >> 1, grp = t / half, off = t % half;
-  const size_t i = (size_t)grp * size + off, j = (size_t)grp * size + size - 1 - off;
+  const uint32_t half = size >> 1, off = t & (half - 1);
+  const size_t base = (size_t)(t & ~(half - 1)) << 1, i = base + off, j = base + size - 1 - off;
   unsigned long long a = keys[i], b = keys[j];
   if (a > b) { keys[i] = b; keys[j] = a; }
 }
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(256) sort_flip_kernel(unsigned long long* __re
 __global__ void __launch_bounds__(256) sort_half_kernel(unsigned long long* __restrict__ keys, uint32_t stride, uint32_t pairs) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= pairs) return;
-  const size_t i = (size_t)2 * stride * (t / stride) + t % stride;
+  const size_t i = ((size_t)(t & ~(stride - 1)) << 1) + (t & (stride - 1));
   unsigned long long a = keys[i], b = keys[i + stride];
   if (a > b) { keys[i] = b; keys[i + stride] = a; }
 }
