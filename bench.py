@@ -116,6 +116,16 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def ncu_traffic(args):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the frame's kernel from the committed `ncu --set full`
+    capture of this same configuration (profiles/r01_tri_vote_summary.txt: 64.78 + 6.86 MB); None for any
+    configuration that was not captured."""
+    if args.workload == "c3" and args.variant == 0 and args.gpus == 1 and args.builder == "host" and \
+            args.spp is None and args.mode is None:
+        return 71634432
+    return None
+
+
 def build_scene(wl, rt):
     if wl["scene"] == "cornell":
         soup = rt.scene_cornell()
@@ -449,7 +459,7 @@ def main():
             "gpu_launches": int(dev.mpm_query(vx.VX_CSR_RT_LAUNCHES)) * K,
             "clocks": r["clocks"],
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": ncu_traffic(args), "peak_source": peak_src,
                          "kernel": "whole vx_start pipeline (trace + shade)", "kernel_ms": r["kern_ms"],
                          "algorithmic_bytes": int(alg_bytes), "nodes_fetched": st["nodes"],
                          "node_bytes": int(node_bytes), "tris_tested": st["tris"]},

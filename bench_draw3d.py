@@ -287,7 +287,10 @@ def native_arm(args, ClockSampler, load_peaks):
                     "binning": "device" if getattr(args, "gpu_binning", False) else "host"},
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "raster_tile_kernel (all draws of a frame)",
+                         # dram bytes read + written by the frame's 10 launches in the committed ncu --set full capture
+                         # of this configuration (profiles/r01_draw3d_ncu_summary.txt: 99.0 + 55.7 MB)
+                         "traffic": 154708736 if (args.trace == "mouse" and args.size == 4096 and world == 1) else None,
+                         "peak_source": peak_src, "kernel": "raster_tile_kernel (all draws of a frame)",
                          "kernel_ms": kern_ms, "algorithmic_bytes": int(alg),
                          "note": "issue-bound integer path; see DESIGN.md section 9 for the issue-slot roofline"},
         }
