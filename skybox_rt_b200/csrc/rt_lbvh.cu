@@ -152,6 +152,32 @@ __global__ void __launch_bounds__(256) sort_half_kernel(unsigned long long* __re
   if (a > b) { keys[i] = b; keys[i + stride] = a; }
 }
 
+// Two global steps per pass over the array (four keys per thread): the flip of stage `size` together with its
+// first half-cleaner (stride size / 4) ...
+__global__ void __launch_bounds__(256) sort_flip_half_kernel(unsigned long long* __restrict__ keys, uint32_t size, uint32_t quads) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= quads) return;
+  const uint32_t quarter = size >> 2, off = t & (quarter - 1);
+  const size_t base = (size_t)(t & ~(quarter - 1)) << 2;  // start of this thread's group of `size` keys
+  const size_t e0 = base + off, e1 = e0 + quarter, m0 = base + size - 1 - off, m1 = m0 - quarter;
+  unsigned long long a = keys[e0], b = keys[e1], c = keys[m1], d = keys[m0];
+  cmpx(a, d); cmpx(b, c);  // flip: i against its mirror
+  cmpx(a, b); cmpx(c, d);  // stride size / 4 inside each half
+  keys[e0] = a; keys[e1] = b; keys[m1] = c; keys[m0] = d;
+}
+
+// ... and two consecutive half-cleaners (strides `stride` and `stride / 2`).
+__global__ void __launch_bounds__(256) sort_half2_kernel(unsigned long long* __restrict__ keys, uint32_t stride, uint32_t quads) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= quads) return;
+  const uint32_t h = stride >> 1, off = t & (h - 1);
+  const size_t i0 = ((size_t)(t & ~(h - 1)) << 2) + off, i1 = i0 + h, i2 = i0 + stride, i3 = i2 + h;
+  unsigned long long a = keys[i0], b = keys[i1], c = keys[i2], d = keys[i3];
+  cmpx(a, c); cmpx(b, d);
+  cmpx(a, b); cmpx(c, d);
+  keys[i0] = a; keys[i1] = b; keys[i2] = c; keys[i3] = d;
+}
+
 __global__ void __launch_bounds__(512) sort_local_halves_kernel(unsigned long long* __restrict__ keys) {
   __shared__ unsigned long long s[kChunk];
   unsigned long long* g = keys + (size_t)blockIdx.x * kChunk;
@@ -165,10 +191,25 @@ int sort_keys(cudaStream_t st, unsigned long long* keys, uint32_t npow2) {
   if (npow2 < kChunk) return -1;  // the caller pads to at least one chunk
   const uint32_t chunks = npow2 / kChunk, pairs = npow2 / 2;
   sort_local_kernel<<<chunks, 512, 0, st>>>(keys);
+  const uint32_t quads = npow2 / 4;
   for (uint32_t size = 2 * kChunk; size != 0 && size <= npow2; size <<= 1) {
-    sort_flip_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(keys, size, pairs);
-    for (uint32_t stride = size >> 2; stride >= kChunk; stride >>= 1)
-      sort_half_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(keys, stride, pairs);
+    // steps of this stage that reach across chunks: the flip, then strides size/4 ... kChunk; two per launch
+    uint32_t stride = size >> 2;
+    if (stride >= kChunk) {
+      sort_flip_half_kernel<<<(quads + 255) / 256, 256, 0, st>>>(keys, size, quads);
+      stride >>= 1;
+    } else {
+      sort_flip_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(keys, size, pairs);
+    }
+    while (stride >= kChunk) {
+      if ((stride >> 1) >= kChunk) {
+        sort_half2_kernel<<<(quads + 255) / 256, 256, 0, st>>>(keys, stride, quads);
+        stride >>= 2;
+      } else {
+        sort_half_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(keys, stride, pairs);
+        stride >>= 1;
+      }
+    }
     sort_local_halves_kernel<<<chunks, 512, 0, st>>>(keys);
   }
   VX_CUDA_OK(cudaGetLastError());

@@ -145,6 +145,11 @@ int vx_dev_close(vx_device_h hdevice) {
   srt::raster_destroy(dev);
   while (dev->buffers) destroy_buffer(dev->buffers);  // apps leak their per-draw args buffers
   cudaStreamSynchronize(dev->stream);                 // the frees are stream-ordered
+  {  // hand the pool's cached memory back: another library in this process (torch) may want it
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev->cuda_dev) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+    cudaGetLastError();
+  }
   cudaEventDestroy(dev->ev_start);
   cudaEventDestroy(dev->ev_stop);
   cudaStreamDestroy(dev->stream);
