@@ -116,6 +116,15 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def weak_frame(w0, h0, n):
+    """Frame of n x the pixels of w0 x h0 at (nearly) the same aspect: the height a multiple of n row blocks so
+    that every rank owns the same number of rows, the width a multiple of the 8-pixel job tile."""
+    unit = ROWS_PER_BLOCK * n
+    h = max(unit, int(round(h0 * n ** 0.5 / unit)) * unit)
+    w = max(8, int(round(w0 * h0 * n / h / 8)) * 8)
+    return w, h
+
+
 def ncu_traffic(args):
     """dram__bytes_read.sum + dram__bytes_write.sum of the frame's kernel from the committed `ncu --set full`
     capture of this same configuration (profiles/r01_tri_vote_summary.txt: 64.78 + 6.86 MB); None for any
@@ -413,10 +422,8 @@ def main():
         # weak scaling: the same view at sqrt(N) x the resolution in each direction, rows interleaved over the
         # N ranks -- pixels (= jobs), samples and so rays per GPU stay those of the 1-GPU frame while the whole
         # job grows N-fold.  The height is rounded so that every rank owns the same number of row blocks.
-        n, w0, h0 = args.gpus, wl["w"], wl["h"]
-        unit = ROWS_PER_BLOCK * n
-        wl["h"] = max(unit, int(round(h0 * n ** 0.5 / unit)) * unit)
-        wl["w"] = max(8, int(round(w0 * h0 * n / wl["h"] / 8)) * 8)
+        n = args.gpus
+        wl["w"], wl["h"] = weak_frame(wl["w"], wl["h"], n)
         wl["name"] += f" [weak scaling: {n} x the pixels, {wl['w']}x{wl['h']}]"
     if args.impl == "reference":
         reference_arm(args, wl)

@@ -85,3 +85,18 @@ def test_raster_tile_rows_gathered_over_gloo(tmp_path, native, world, w, h, port
     mp.spawn(_raster_worker, args=(world, port, w, h, out), nprocs=world, join=True)
     full, _, _ = od.render(od.oracle(), od.trace_blob("vase"), w, h, threads=1)
     assert np.array_equal(np.load(out), full)
+
+
+def test_weak_scaling_frames_keep_the_work_per_rank():
+    """bench.py's weak scaling: N x the pixels of the 1-GPU frame, the same rows for every rank."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    from skybox_rt_b200.formats import rank_rows
+    for n in (2, 3, 4, 8):
+        w, h = bench.weak_frame(1920, 1080, n)
+        rows = [rank_rows(h, bench.ROWS_PER_BLOCK, n, r) for r in range(n)]
+        assert len(set(rows)) == 1 and sum(rows) == h
+        assert abs(w * h / (1920 * 1080 * n) - 1) < 0.005 and w % 8 == 0
+        assert abs((w / h) / (1920 / 1080) - 1) < 0.03
