@@ -87,11 +87,15 @@ __global__ void __launch_bounds__(256) lbvh_keys_kernel(const srt_triangle_t* __
   if (i >= npow2) return;
   if (i >= n) { keys[i] = ~0ull; return; }  // padding sorts to the end and never moves
   const Box b = tri_box(load_tri(soup, i));
+  // one scale for the three axes (the largest extent): Morton cells are cubes, so a flat scene spends its bits on
+  // the two axes it extends along instead of slicing itself into thin layers
+  float ext = 0.0f;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) ext = fmaxf(ext, o2f(scene[3 + k]) - o2f(scene[k]));
   uint32_t q[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    const float lo = o2f(scene[k]), hi = o2f(scene[3 + k]);
-    const float ext = hi - lo, c = (b.lo[k] + b.hi[k]) * 0.5f;
+    const float lo = o2f(scene[k]), c = (b.lo[k] + b.hi[k]) * 0.5f;
     float g = ext > 0.0f ? ((c - lo) / ext) * 1024.0f : 0.0f;
     g = fminf(fmaxf(g, 0.0f), 1023.0f);  // NaN -> 0
     q[k] = (uint32_t)g;
