@@ -338,6 +338,7 @@ __global__ void __launch_bounds__(PPT == 4 ? kRasterThreads : 1024) raster_tile_
     B.dst_rgb = P.bl_dst_rgb; B.dst_a = P.bl_dst_a;
   }
   __shared__ int32_t s_prims[kPrimChunk][30];  // rast_prim_t = 30 words
+  __shared__ uint32_t s_mask[kPrimChunk];      // per staged primitive: which 8x8 blocks of the tile survive levels 5..3
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   // tile header (gpu_sw.h:38-45)
@@ -382,6 +383,8 @@ __global__ void __launch_bounds__(PPT == 4 ? kRasterThreads : 1024) raster_tile_
     }
   }
 
+  const uint32_t my_bit = 1u << (((ly >> 3) << 2) | (lx >> 3));         // the 8x8 block of this thread's quad / pixel
+  const uint32_t warp_bits = __reduce_or_sync(0xffffffffu, my_bit);    // one block (PPT 1) or two (PPT 4)
   unsigned long long n_frag = 0, n_tested = 0;
   uint32_t n_om_rd = 0;
   if (STATS) n_om_rd = (uint32_t)__popc(inside) * ((need_ds ? 1u : 0u) + (need_col ? 1u : 0u));
@@ -396,34 +399,53 @@ __global__ void __launch_bounds__(PPT == 4 ? kRasterThreads : 1024) raster_tile_
     }
     __syncthreads();
 
-    for (uint32_t k = 0; k < n; ++k) {
-      const int32_t* pr = s_prims[k];
-      // edges e[i] = (a, b, c) at pr[3i .. 3i+2]; int32 wrap-around arithmetic throughout
-      // renderTile / renderQuad rejection for this quad's ancestors (graphics.cpp:749-753, :805-809):
-      // value at the ancestor's origin + (extent << level) < 0 on any edge.  Levels 5 (tile) and 4 (16x16
-      // block) are the same for all lanes of a warp, so a warp leaves the primitive here without diverging.
-      uint32_t reject = 0, ext[3];
+    // Block masks: the reference's renderTile recursion rejects a block when value(origin) + (extent << level) < 0 on
+    // any edge (graphics.cpp:749-753), at level 5 (the tile), 4 (16x16) and 3 (8x8) before it reaches the quads.
+    // Those tests depend on the block only, so sixteen threads per primitive evaluate them once for the sixteen 8x8
+    // blocks of the tile -- same int32 wrap-around expressions -- and every warp then drops a primitive that misses
+    // its blocks with one shared-memory word instead of redoing the edge arithmetic.
+    for (uint32_t w0 = 0; w0 < n * 16u; w0 += NT) {
+      const uint32_t w = w0 + tid;
+      bool pass = false;
+      if (w < n * 16u) {
+        const int32_t* pr = s_prims[w >> 4];
+        const uint32_t bx = w & 3u, by = (w >> 2) & 3u;
+        uint32_t rej = 0;
 #pragma unroll
-      for (int i = 0; i < 3; ++i) {
-        const uint32_t a = (uint32_t)pr[3 * i], b = (uint32_t)pr[3 * i + 1], c = (uint32_t)pr[3 * i + 2];
-        const int32_t sa = (int32_t)a, sb = (int32_t)b;
-        ext[i] = (sb >= 0) ? ((sa >= 0) ? a + b : b) : ((sa >= 0) ? a : 0u);  // CalcEdgeExtents (graphics.cpp:644-647)
-#pragma unroll
-        for (int L = RASTER_TILE_LOGSIZE; L >= RASTER_TILE_LOGSIZE - 1; --L) {
-          const uint32_t ox = X0 + (lx & ~((1u << L) - 1)), oy = Y0 + (ly & ~((1u << L) - 1));
-          reject |= (a * ox + b * oy + c + (ext[i] << L)) >> 31;
+        for (int i = 0; i < 3; ++i) {
+          const uint32_t a = (uint32_t)pr[3 * i], b = (uint32_t)pr[3 * i + 1], c = (uint32_t)pr[3 * i + 2];
+          const int32_t sa = (int32_t)a, sb = (int32_t)b;
+          const uint32_t ext = (sb >= 0) ? ((sa >= 0) ? a + b : b) : ((sa >= 0) ? a : 0u);  // CalcEdgeExtents (graphics.cpp:644-647)
+          rej |= (a * X0 + b * Y0 + c + (ext << 5)) >> 31;
+          rej |= (a * (X0 + ((bx >> 1) << 4)) + b * (Y0 + ((by >> 1) << 4)) + c + (ext << 4)) >> 31;
+          rej |= (a * (X0 + (bx << 3)) + b * (Y0 + (by << 3)) + c + (ext << 3)) >> 31;
         }
+        pass = rej == 0;
       }
+      const uint32_t bal = __ballot_sync(0xffffffffu, pass);
+      if (w < n * 16u && (lane & 15u) == 0u) s_mask[w >> 4] = (bal >> (lane & 16u)) & 0xffffu;
+    }
+    __syncthreads();
+
+    for (uint32_t k = 0; k < n; ++k) {
+      const uint32_t blocks = s_mask[k];
       if (STATS) ++n_tested;
-      if (reject) continue;
+      if (!(blocks & warp_bits)) continue;  // warp-uniform: the primitive misses every block this warp covers
+      if (!(blocks & my_bit)) continue;     // levels 5, 4, 3 of this thread's own ancestors
+      const int32_t* pr = s_prims[k];
+      // edges e[i] = (a, b, c) at pr[3i .. 3i+2]; int32 wrap-around arithmetic throughout.  The remaining levels of
+      // the recursion (4x4 block, the quad: graphics.cpp:805-809) differ per thread.
+      uint32_t reject = 0;
       int32_t eq[3];  // edge values at the quad's top-left pixel
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
         const uint32_t a = (uint32_t)pr[3 * i], b = (uint32_t)pr[3 * i + 1], c = (uint32_t)pr[3 * i + 2];
+        const int32_t sa = (int32_t)a, sb = (int32_t)b;
+        const uint32_t ext = (sb >= 0) ? ((sa >= 0) ? a + b : b) : ((sa >= 0) ? a : 0u);
 #pragma unroll
-        for (int L = RASTER_TILE_LOGSIZE - 2; L >= 1; --L) {
+        for (int L = RASTER_TILE_LOGSIZE - 3; L >= 1; --L) {
           const uint32_t ox = X0 + (lx & ~((1u << L) - 1)), oy = Y0 + (ly & ~((1u << L) - 1));
-          reject |= (a * ox + b * oy + c + (ext[i] << L)) >> 31;
+          reject |= (a * ox + b * oy + c + (ext << L)) >> 31;
         }
         eq[i] = (int32_t)(a * px + b * py + c);
       }
