@@ -288,8 +288,8 @@ def native_arm(args, ClockSampler, load_peaks):
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          # dram bytes read + written by the frame's 10 launches in the committed ncu --set full capture
-                         # of this configuration (profiles/r01_draw3d_ncu_summary.txt: 99.0 + 55.7 MB)
-                         "traffic": 154708736 if (args.trace == "mouse" and args.size == 4096 and world == 1) else None,
+                         # of this configuration (profiles/r01_draw3d_ncu_summary.txt: 99.0 + 55.6 MB)
+                         "traffic": 154599424 if (args.trace == "mouse" and args.size == 4096 and world == 1) else None,
                          "peak_source": peak_src, "kernel": "raster_tile_kernel (all draws of a frame)",
                          "kernel_ms": kern_ms, "algorithmic_bytes": int(alg),
                          "note": "issue-bound integer path; see DESIGN.md section 9 for the issue-slot roofline"},
