@@ -56,6 +56,8 @@ def parse():
                     help="diagnostic: VX_DCR_RT_SPLIT_SAMPLES (0 = split multi-sample frames into per-sample jobs, 1 = never)")
     ap.add_argument("--builder", default="host", choices=["host", "device"],
                     help="RT: BVH from the host binned-SAH builder (default) or built on the device (vx_cuda_rt_build_lbvh)")
+    ap.add_argument("--device-clear", action="store_true",
+                    help="draw3d: e2e leg clears the targets on the device (vx_cuda_fill32) instead of the reference's host upload")
     ap.add_argument("--gpu-binning", action="store_true",
                     help="draw3d: e2e leg bins on the device (vx_cuda_draw3d_binning) instead of the host pre-pass")
     ap.add_argument("--ppt", type=int, default=0, help="draw3d diagnostic: force pixels per thread (4 or 1; 0 = by grid size)")

@@ -202,7 +202,9 @@ def native_arm(args, ClockSampler, load_peaks):
 
     # ---- e2e: the reference app's loop with host buffers, wall clock -------------------------------
     host_frame = torch.empty(H * W, dtype=torch.int32).pin_memory()
-    app2 = d3.Draw3D(W, H, flags=ALL_SW | d3.WIDE_TILES | (d3.GPU_BINNING if getattr(args, "gpu_binning", False) else 0),
+    device_clear = getattr(args, "device_clear", False)
+    app2 = d3.Draw3D(W, H, flags=ALL_SW | d3.WIDE_TILES | (d3.GPU_BINNING if getattr(args, "gpu_binning", False) else 0) |
+                     (d3.DEVICE_CLEAR if device_clear else 0),
                      rank=rank, num_ranks=world, device=dev)
     c2addr, _ = app2.buffer_addresses()
     cbuf2 = torch.as_tensor(DevMem(c2addr, W * H * 4), device="cuda").view(H, W)
@@ -227,7 +229,7 @@ def native_arm(args, ClockSampler, load_peaks):
     barrier()
     e2e_s = (time.perf_counter() - t0) / e2e_steps
     st2 = app2.stats()
-    h2d = st2["h2d_bytes"] + 2 * W * H * 4  # per-draw uploads + the two clear uploads
+    h2d = st2["h2d_bytes"] + (0 if device_clear else 2 * W * H * 4)  # per-draw uploads + the two clear uploads
     d2h = W * H * 4 if rank == 0 else 0
     app2.close()
 
@@ -284,7 +286,8 @@ def native_arm(args, ClockSampler, load_peaks):
             "e2e": {"value": frags_total / e2e_s / 1e6, "unit": "Mfragments/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_s * 1e3,
                     "host_ms": {"binning": st2["bin_ms"], "upload": st2["upload_ms"], "start+wait": st2["run_ms"]},
-                    "binning": "device" if getattr(args, "gpu_binning", False) else "host"},
+                    "binning": "device" if getattr(args, "gpu_binning", False) else "host",
+                    "clear": "device fill" if device_clear else "host upload (the reference app's flow)"},
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          # dram bytes read + written by the frame's 10 launches in the committed ncu --set full capture

@@ -84,6 +84,12 @@ int vx_cuda_rt_build_lbvh(vx_device_h hdevice, vx_buffer_h soup, uint32_t num_tr
  * tests and tooling: *size = its size in bytes; copied to dst when dst != NULL and capacity suffices. */
 int vx_cuda_rt_node4_image(vx_device_h hdevice, void* dst, uint64_t capacity, uint64_t* size);
 
+/* Fill `size` bytes of a buffer at `offset` with a 32-bit pattern on the device (both multiples of 4), ordered on the
+ * launch stream.  The reference's apps clear their render targets by uploading a host array of the clear value
+ * (draw3d/main.cpp:478-490: 2 x W x H x 4 bytes over the host link per frame); an app that knows it runs on this
+ * back-end clears here instead. */
+int vx_cuda_fill32(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, uint32_t value);
+
 /* CUDA device ordinal the handle was opened on. */
 int vx_cuda_device(vx_device_h hdevice, int* ordinal);
 

@@ -272,7 +272,14 @@ void srt_draw3d_close(srt_draw3d_t* r) { /* cleanup(), main.cpp:137-146 (the dev
 }
 
 int srt_draw3d_clear(srt_draw3d_t* r) { /* main.cpp:478-490 */
-  int rc = vx_copy_to_dev(r->depth_buffer, r->clear_z, 0, r->zbuf_size);
+  int rc;
+  if (r->flags & SRT_DRAW3D_DEVICE_CLEAR) {
+    rc = vx_cuda_fill32(r->depth_buffer, 0, r->zbuf_size, 0xffffffffu);
+    if (rc == 0) rc = vx_cuda_fill32(r->color_buffer, 0, r->cbuf_size, 0xff000000u);
+    r->stats.h2d_bytes = 0;
+    return rc;
+  }
+  rc = vx_copy_to_dev(r->depth_buffer, r->clear_z, 0, r->zbuf_size);
   if (rc == 0) rc = vx_copy_to_dev(r->color_buffer, r->clear_c, 0, r->cbuf_size);
   r->stats.h2d_bytes = r->zbuf_size + r->cbuf_size;
   return rc;

@@ -29,6 +29,8 @@ extern "C" {
 #define SRT_DRAW3D_SW_OM 0x2   /* -y */
 #define SRT_DRAW3D_SW_TEX 0x4  /* -u */
 #define SRT_DRAW3D_WIDE_TILES 0x8 /* 32-bit tile headers (needed beyond ~64 K tile-primitive pairs) */
+#define SRT_DRAW3D_DEVICE_CLEAR 0x20 /* srt_draw3d_clear fills the targets on the device (vx_cuda_fill32) instead of
+                                        uploading two host arrays of the clear values like the reference app */
 #define SRT_DRAW3D_GPU_BINNING 0x10 /* triangle setup + binning on the device (vx_cuda_draw3d_binning): vertices and
                                        indices are uploaded instead of primbuf / tilebuf; same bytes, same frame */
 

@@ -497,6 +497,43 @@ int vx_cuda_stream(vx_device_h hdevice, void** stream) {
   return 0;
 }
 
+namespace {
+__global__ void __launch_bounds__(256) fill32_kernel(uint4* __restrict__ dst, uint64_t n16, uint32_t* __restrict__ tail,
+                                                     uint32_t ntail, uint32_t v) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint4 vv = make_uint4(v, v, v, v);
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) dst[i] = vv;
+  if (blockIdx.x == 0 && threadIdx.x < ntail) tail[threadIdx.x] = v;
+}
+}  // namespace
+
+int vx_cuda_fill32(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, uint32_t value) {
+  if (nullptr == hbuffer) return -1;
+  vx_buffer* b = as_buf(hbuffer);
+  if ((offset | size) & 3u || offset + size > b->size) return -1;
+  if (size == 0) return 0;
+  vx_device* dev = b->dev;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  char* p = (char*)b->dptr + offset;
+  // words up to the first 16-byte boundary and after the last one go through the tail path
+  uint64_t head = (16 - ((uintptr_t)p & 15)) & 15;
+  if (head > size) head = size;
+  if (head) fill32_kernel<<<1, 32, 0, dev->stream>>>(nullptr, 0, (uint32_t*)p, (uint32_t)(head / 4), value);
+  const uint64_t n16 = (size - head) / 16, rest = (size - head) % 16;
+  if (n16 || rest) {
+    const uint64_t want = (n16 + 255) / 256;
+    const unsigned grid = (unsigned)(want < 1 ? 1 : (want > 148ull * 16 ? 148ull * 16 : want));
+    fill32_kernel<<<grid, 256, 0, dev->stream>>>((uint4*)(p + head), n16, (uint32_t*)(p + head + n16 * 16),
+                                                 (uint32_t)(rest / 4), value);
+  }
+  VX_CUDA_OK(cudaGetLastError());
+  b->generation++;
+  if (b->shadow) {
+    for (uint64_t i = 0; i < size / 4; ++i) memcpy(b->shadow + offset + 4 * i, &value, 4);
+  }
+  return 0;
+}
+
 int vx_cuda_host_register(vx_device_h hdevice, void* ptr, uint64_t size) {
   if (nullptr == hdevice || nullptr == ptr || 0 == size) return -1;
   cudaSetDevice(as_dev(hdevice)->cuda_dev);

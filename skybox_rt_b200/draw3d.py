@@ -17,7 +17,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 APP_LIB = os.path.join(PKG, "lib", "libdraw3d_app.so")
 HOST_LIB = os.path.join(PKG, "lib", "libskybox_rt_host.so")
 
-SW_RAST, SW_OM, SW_TEX, WIDE_TILES, GPU_BINNING = 1, 2, 4, 8, 16
+SW_RAST, SW_OM, SW_TEX, WIDE_TILES, GPU_BINNING, DEVICE_CLEAR = 1, 2, 4, 8, 16, 32
 TILEBUF_REFERENCE, TILEBUF_WIDE = 0, 1
 VX_CSR_RASTER_FRAGMENTS, VX_CSR_RASTER_QUAD_TESTS, VX_CSR_RASTER_TILES = 0x7C8, 0x7C9, 0x7CA
 VX_DCR_RASTER_EXT_TBUF_FORMAT = 0x804

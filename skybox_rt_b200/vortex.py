@@ -43,7 +43,7 @@ EXPORTS = [
 ]
 CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx_cuda_host_unregister",
                 "vx_cuda_perf_totals", "vx_cuda_draw3d_binning", "vx_cuda_rt_build_lbvh",
-                "vx_cuda_rt_node4_image"]  # include/vortex_cuda.h
+                "vx_cuda_rt_node4_image", "vx_cuda_fill32"]  # include/vortex_cuda.h
 
 _lib = None
 
@@ -82,6 +82,7 @@ def lib():
             "vx_cuda_perf_totals": [vp, C.POINTER(u64), u32],
             "vx_cuda_rt_build_lbvh": [vp, vp, u32, C.POINTER(vp), C.POINTER(vp), vp],
             "vx_cuda_rt_node4_image": [vp, vp, u64, C.POINTER(u64)],
+            "vx_cuda_fill32": [vp, u64, u64, u32],
             "vx_cuda_draw3d_binning": [vp, vp, u32, vp, u32, C.c_float, C.c_float, u32, u32, u32, u32, u32, u32,
                                        C.POINTER(vp), C.POINTER(vp), vp],
         }
@@ -130,6 +131,10 @@ class Buffer:
         p, n = _host_ptr(dst)
         _check(lib().vx_copy_from_dev(p, self.handle, offset, n), "vx_copy_from_dev")
         return dst
+
+    def fill32(self, value, offset=0, size=None):
+        """Device-side fill with a 32-bit pattern (vx_cuda_fill32)."""
+        _check(lib().vx_cuda_fill32(self.handle, offset, self.size - offset if size is None else size, value), "vx_cuda_fill32")
 
     def free(self):
         if self.handle is not None:

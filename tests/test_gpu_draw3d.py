@@ -220,3 +220,29 @@ def test_pixel_per_thread_kernel_equals_quad_per_thread_kernel(d3, name):
             app.dev.dcr_write(0x806, ppt)  # VX_DCR_RASTER_EXT_PPT
             frames.append(app.frame(t, depth=True))
     assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])
+
+
+def test_device_fill_and_device_clear(d3):
+    """vx_cuda_fill32 (any 4-byte aligned range) and the app's device-side clear give the host-upload clear's frame."""
+    from skybox_rt_b200 import vortex as vx
+    with vx.Device() as dev:
+        n = 1000
+        buf = dev.alloc(n * 4)
+        base = np.arange(n, dtype=np.uint32)
+        for off, cnt, val in [(0, n, 0xff000000), (1, 1, 7), (3, 10, 0xdeadbeef), (5, 123, 1), (997, 3, 2), (4, 0, 9)]:
+            buf.write(base)
+            buf.fill32(val, off * 4, cnt * 4)
+            want = base.copy()
+            want[off:off + cnt] = val
+            assert np.array_equal(buf.read(np.empty(n, np.uint32)), want), (off, cnt)
+        for bad in [(2, 4), (0, 6), (0, n * 4 + 4)]:
+            with pytest.raises(vx.VortexError):
+                buf.fill32(0, *bad)
+        buf.free()
+    t = d3.Trace(blob=od.trace_blob("vase"))
+    with d3.Draw3D(200, 120, flags=ALL_SW) as app:
+        want_c, want_z = app.frame(t), app.read(depth=True)
+    with d3.Draw3D(200, 120, flags=ALL_SW | d3.DEVICE_CLEAR) as app:
+        for _ in range(2):  # the second frame starts from a dirty target
+            got_c, got_z = app.frame(t), app.read(depth=True)
+    assert np.array_equal(got_c, want_c) and np.array_equal(got_z, want_z)
