@@ -471,7 +471,10 @@ def main():
                          "frac": achieved / peak, "traffic": ncu_traffic(args), "peak_source": peak_src,
                          "kernel": "whole vx_start pipeline (trace + shade)", "kernel_ms": r["kern_ms"],
                          "algorithmic_bytes": int(alg_bytes), "nodes_fetched": st["nodes"],
-                         "node_bytes": int(node_bytes), "tris_tested": st["tris"]},
+                         "node_bytes": int(node_bytes), "tris_tested": st["tris"],
+                         "note": "algorithmic bytes are mostly served by L1/L2 (the C3 scene is L2-resident): the kernel is "
+                                 "bound by issue slots x lanes per instruction, not by HBM -- ncu: 66 % issue-active at "
+                                 "14.2 of 32 lanes (profiles/r01_tri_vote_summary.txt, DESIGN.md section 4)"},
             "host_prepass_s": {"bvh2_build": r["build_s"]},
             "builder": args.builder, "device_open_upload_build_ms": r.get("device_build_ms"),
         }
