@@ -188,3 +188,21 @@ def test_c_reader_rejects_malformed_archives(d3, tmp_path):
         p.write_bytes(bad)
         with pytest.raises(vx.VortexError):
             d3.Trace(path=str(p))
+
+
+def test_draw_arrays_expose_the_trace_geometry(d3):
+    """Trace.draw_arrays (the input of the device pre-pass) = the vertex / index arrays of the flat trace blob."""
+    import struct
+    blob = od.trace_blob("box")
+    t = d3.Trace(blob=blob)
+    _, draws = od._walk(blob)
+    for d, off in enumerate(draws):
+        near, far = struct.unpack_from("<2f", blob, off + 112 + 4 + 16)
+        nv, npr = struct.unpack_from("<II", blob, off + 112 + 4 + 24)
+        v, p, n, f = t.draw_arrays(d)
+        assert v.shape == (nv, 10) and p.shape == (npr, 3) and (n, f) == (near, far)
+        base = off + 112 + 4 + 24 + 8
+        assert v.tobytes() == blob[base:base + nv * 40] and p.tobytes() == blob[base + nv * 40:base + nv * 40 + npr * 12]
+        assert p.max() < nv
+    with pytest.raises(IndexError):
+        t.draw_arrays(len(draws))
