@@ -86,8 +86,9 @@ int vx_dev_caps(vx_device_h hdevice, uint32_t caps_id, uint64_t* value);
 
 /* ---- memory --------------------------------------------------------------------- */
 
-/* reference vortex.h:83, callbacks.inc:57-78.  cudaMalloc, 256 B aligned (>= the
- * reference's 64 B block alignment).  size 0 or NULL handle -> -1. */
+/* reference vortex.h:83, callbacks.inc:57-78.  From the device's stream-ordered pool
+ * (cudaMallocAsync on the launch stream), 256 B aligned (>= the reference's 64 B block
+ * alignment).  size 0 or NULL handle -> -1. */
 int vx_mem_alloc(vx_device_h hdevice, uint64_t size, int flags, vx_buffer_h* hbuffer);
 
 /* reference vortex.h:86.  Fixed-address reservations have no meaning for CUDA virtual
@@ -95,7 +96,9 @@ int vx_mem_alloc(vx_device_h hdevice, uint64_t size, int flags, vx_buffer_h* hbu
  * *reported* address only for kernel images (used by vx_upload_kernel_bytes). */
 int vx_mem_reserve(vx_device_h hdevice, uint64_t address, uint64_t size, int flags, vx_buffer_h* hbuffer);
 
-/* reference vortex.h:89, callbacks.inc:98-110.  NULL is a successful no-op. */
+/* reference vortex.h:89, callbacks.inc:98-110.  NULL is a successful no-op.  The free is
+ * ordered behind the work already queued on the launch stream, so it neither waits for a
+ * running kernel nor pulls the memory from under it. */
 int vx_mem_free(vx_buffer_h hbuffer);
 
 /* reference vortex.h:92.  Range-checked; access rights are recorded, not enforced. */
