@@ -132,8 +132,12 @@ int vx_ready_wait(vx_device_h hdevice, uint64_t timeout);
 int vx_dcr_read(vx_device_h hdevice, uint32_t addr, uint32_t* value);
 int vx_dcr_write(vx_device_h hdevice, uint32_t addr, uint32_t value);
 
-/* reference vortex.h:119.  addr = VX_CSR_MCYCLE / VX_CSR_MINSTRET / VX_CSR_RT_* (see
- * skybox_rt.h); core_id 0xffffffff sums over cores like the reference does. */
+/* reference vortex.h:119, simx/vortex.cpp:224-236: the value of ONE core, no summing (vx_dump_perf adds them up,
+ * stub/utils.cpp:159-805).  core_id = SM index; core_id >= VX_CAPS_NUM_CORES returns -1.  VX_CSR_MINSTRET is the
+ * work started on that SM (performance monitor on) or the run's total on core 0 and 0 elsewhere (monitor off), so
+ * the sum over cores is the total either way; VX_CSR_MCYCLE and the class CSRs 0xB03.. read the same on every
+ * core (device-wide units, like the reference's shared raster / tex / om units); the back-end CSRs VX_CSR_RT_* /
+ * VX_CSR_RASTER_* (skybox_rt.h, skybox_draw3d.h) are device totals of the last vx_start on every core. */
 int vx_mpm_query(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t* value);
 
 /* ---- utilities (reference vortex.h:124-139, stub/utils.cpp:49-155, :159, :807) ---- */

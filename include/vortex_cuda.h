@@ -90,6 +90,12 @@ int vx_cuda_rt_node4_image(vx_device_h hdevice, void* dst, uint64_t capacity, ui
  * back-end clears here instead. */
 int vx_cuda_fill32(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, uint32_t value);
 
+/* Read-bandwidth probe for roofline denominators measured on the box a benchmark runs on: #SM x 8 CTAs stream
+ * `bytes` (a multiple of 16) of a private device buffer `repeats` times with 16-byte read-only loads, after one
+ * untimed pass; *ms = device time of the timed passes (CUDA events on the launch stream).  bytes well inside the
+ * L2 (<= 64 MiB on B200) measures L2 -> SM bandwidth, bytes far beyond it (>= 1 GiB) HBM read bandwidth. */
+int vx_cuda_probe_read_bandwidth(vx_device_h hdevice, uint64_t bytes, uint32_t repeats, float* ms);
+
 /* CUDA device ordinal the handle was opened on. */
 int vx_cuda_device(vx_device_h hdevice, int* ordinal);
 

@@ -31,6 +31,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-Wall",
     "-I", INC, "-I", CSRC,
 ]
+NCCL_LINK = []  # filled in when the NCCL frame gather is built in (csrc/vx_nccl.cu)
 HOST_CFLAGS = ["-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-Wall", "-Wextra", "-I", INC]
 
 
@@ -82,7 +83,15 @@ def build(force=False, verbose=False):
     cu_src = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cpp"))]
     vx_so = os.path.join(LIB, "libvortex.so")
     if force or _stale(vx_so, cu_src + headers):
-        _run([NVCC] + NVCC_FLAGS + ["-shared", "-o", vx_so] + cu_src, verbose)
+        # one object per translation unit, compiled side by side (objects live in the git-ignored build/)
+        from concurrent.futures import ThreadPoolExecutor
+        obj_dir = os.path.join(PKG, "build")
+        os.makedirs(obj_dir, exist_ok=True)
+        objs = [os.path.join(obj_dir, os.path.basename(f) + ".o") for f in cu_src]
+        todo = [(f, o) for f, o in zip(cu_src, objs) if force or _stale(o, [f] + headers)]
+        with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+            list(ex.map(lambda fo: _run([NVCC] + NVCC_FLAGS + ["-c", fo[0], "-o", fo[1]], verbose), todo))
+        _run([NVCC, "-shared", "-o", vx_so] + objs + NCCL_LINK, verbose)
     plugin = os.path.join(LIB, "libvortex-cuda.so")
     if force or _stale(plugin, [vx_so]):
         shutil.copyfile(vx_so, plugin)

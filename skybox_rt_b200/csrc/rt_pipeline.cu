@@ -15,6 +15,7 @@
 #include "rt_baseline.cuh"
 #include "rt_wide.cuh"
 #include "rt_pool.cuh"
+#include "rt_wave.cuh"
 // clang-format on
 
 namespace srt {
@@ -25,7 +26,8 @@ namespace srt {
 // draw call (tests/regression/draw3d/main.cpp:190-211), except that the B200 layout is derived by
 // the back-end instead of being uploaded by the app.
 struct WideCache {
-  uint64_t node_addr, tri_addr, generation;
+  uint64_t node_addr, tri_addr;
+  uint64_t node_uid, tri_uid, node_gen, tri_gen;  // which allocations, and which contents of them
   uint32_t num_nodes, num_tris;
   float4* d_nodes4;
   uint32_t num_nodes4, depth;
@@ -42,6 +44,11 @@ struct RtState {
   size_t spill_warps;
   float4* d_samples;               // per-sample radiance of split multi-sample frames, [spp][pixels]
   size_t samples_capacity;         // in float4
+  // wavefront pipeline (rt_wave.cuh): queues and path state for `wave_jobs` jobs, one allocation
+  char* d_wave;
+  uint64_t wave_jobs;
+  WaveBufs wave;
+  int wave_blocks_per_sm[12];      // occupancy per (stage, scheduler, stats) instantiation
 };
 
 static int rt_state(vx_device* dev, RtState** out) {
@@ -75,7 +82,8 @@ static int wide_prepare(vx_device* dev, RtState* st, const kernel_arg_t& a) {
   }
   WideCache& c = st->wide;
   if (c.valid && c.node_addr == a.node_addr && c.tri_addr == a.tri_addr && c.num_nodes == a.num_nodes &&
-      c.num_tris == a.num_tris && c.generation == nb->generation + tb->generation)
+      c.num_tris == a.num_tris && c.node_uid == nb->uid && c.tri_uid == tb->uid && c.node_gen == nb->generation &&
+      c.tri_gen == tb->generation)
     return 0;
   const srt_bvh2_node_t* d_n2 = reinterpret_cast<const srt_bvh2_node_t*>((const char*)nb->dptr + (a.node_addr - nb->reported_addr));
   const srt_tri_rec_t* d_tr = reinterpret_cast<const srt_tri_rec_t*>((const char*)tb->dptr + (a.tri_addr - tb->reported_addr));
@@ -115,7 +123,8 @@ static int wide_prepare(vx_device* dev, RtState* st, const kernel_arg_t& a) {
   }
   c.d_nodes4 = d_n4;
   c.valid = false;
-  c.node_addr = a.node_addr; c.tri_addr = a.tri_addr; c.generation = nb->generation + tb->generation;
+  c.node_addr = a.node_addr; c.tri_addr = a.tri_addr;
+  c.node_uid = nb->uid; c.tri_uid = tb->uid; c.node_gen = nb->generation; c.tri_gen = tb->generation;
   c.num_nodes = a.num_nodes; c.num_tris = a.num_tris;
   c.num_nodes4 = count4; c.depth = depth;
   c.valid = true;
@@ -162,12 +171,100 @@ static int pool_grid(vx_device* dev, RtState* st, int* cached, K kernel, size_t 
   return grid;
 }
 
+// vx_mem_free of a scene buffer: the stream-ordered pool hands the same address to the next allocation of that
+// size, so the image derived from the freed buffer must not outlive it.
+void rt_buffer_freed(vx_device* dev, const vx_buffer* b) {
+  if (!dev->rt) return;
+  WideCache& c = dev->rt->wide;
+  if (c.valid && (c.node_uid == b->uid || c.tri_uid == b->uid)) c.valid = false;
+}
+
+// ---- wavefront pipeline (variants 4 / 5, rt_wave.cuh) ------------------------------------------------------------
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static int wave_reserve(RtState* st, uint64_t jobs, bool need_sum) {
+  if (st->d_wave && st->wave_jobs >= jobs && (!need_sum || st->wave.sum)) return 0;
+  if (st->d_wave) cudaFree(st->d_wave);  // cudaFree waits for queued work that still reads it
+  st->d_wave = nullptr;
+  st->wave_jobs = 0;
+  const size_t n = (size_t)jobs;
+  const size_t sz_ctl = align256(sizeof(WaveCtl)), sz_hit = align256(n * sizeof(uint2)), sz_path = align256(n * sizeof(float4)),
+               sz_q = align256(n * 2 * sizeof(float4)), sz_sum = need_sum ? align256(n * sizeof(float4)) : 0;
+  const size_t total = sz_ctl + 2 * sz_hit + sz_path + 2 * sz_q + sz_sum;
+  if (cudaMalloc(&st->d_wave, total) != cudaSuccess) {
+    cudaGetLastError();
+    fprintf(stderr, "[VXDRV] raytrace: out of device memory for the ray queues (%zu MB)\n", total >> 20);
+    return -1;
+  }
+  char* p = st->d_wave;
+  st->wave.ctl = reinterpret_cast<WaveCtl*>(p); p += sz_ctl;
+  st->wave.hit1 = reinterpret_cast<uint2*>(p); p += sz_hit;
+  st->wave.hit2 = reinterpret_cast<uint2*>(p); p += sz_hit;
+  st->wave.path = reinterpret_cast<float4*>(p); p += sz_path;
+  st->wave.q_shadow = reinterpret_cast<float4*>(p); p += sz_q;
+  st->wave.q_bounce = reinterpret_cast<float4*>(p); p += sz_q;
+  st->wave.sum = need_sum ? reinterpret_cast<float4*>(p) : nullptr;
+  st->wave_jobs = jobs;
+  return 0;
+}
+
+template <int STAGE, int SCHED, bool STATS>
+static int wave_trace(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, uint32_t rows,
+                      uint32_t jobs, uint32_t s) {
+  const size_t smem = sizeof(uint2) * kSmStack * kWideThreads;
+  int* occ = st->wave_blocks_per_sm + (STAGE * 4 + SCHED * 2 + (STATS ? 1 : 0));
+  auto kernel = rt_wave_trace_kernel<STAGE, SCHED, STATS>;
+  if (*occ == 0) {
+    int n = 0;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kWideThreads, smem) != cudaSuccess || n <= 0)
+      return -1;
+    *occ = n;
+  }
+  // camera stage: no more CTAs than there are jobs; queue stages: the queue size is only known on the device
+  uint64_t grid = (uint64_t)dev->prop.multiProcessorCount * (uint64_t)*occ;
+  if (STAGE == 0) {
+    const uint64_t need = ((uint64_t)jobs + kWideThreads - 1) / kWideThreads;
+    if (need < grid) grid = need;
+  }
+  kernel<<<(unsigned)grid, kWideThreads, smem, dev->stream>>>(a, sc, st->wave, rows, jobs, s, st->d_counters);
+  return 0;
+}
+
+template <int SCHED, bool STATS>
+static int wave_frame(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, uint32_t rows,
+                      uint32_t jobs, uint32_t* launches) {
+  cudaStream_t s = dev->stream;
+  const float4* tris = sc.tris;
+  const unsigned blocks = (jobs + 255u) / 256u;
+  const unsigned sm_blocks = (unsigned)dev->prop.multiProcessorCount * 8u;
+  VX_CUDA_OK(cudaMemsetAsync(st->wave.ctl, 0, sizeof(WaveCtl), s));
+  for (uint32_t sample = 0; sample < a.spp; ++sample) {
+    if (wave_trace<0, SCHED, STATS>(dev, st, a, sc, rows, jobs, sample) != 0) return -1;
+    rt_wave_shade1_kernel<<<blocks, 256, 0, s>>>(a, tris, st->wave, rows, jobs, sample);
+    *launches += 2;
+    if (a.mode >= SRT_MODE_SHADOW) {
+      if (wave_trace<1, SCHED, STATS>(dev, st, a, sc, rows, jobs, sample) != 0) return -1;
+      *launches += 1;
+    }
+    if (a.mode >= SRT_MODE_BOUNCE) {
+      rt_wave_shade2_kernel<<<blocks < sm_blocks ? blocks : sm_blocks, 256, 0, s>>>(a, tris, st->wave);
+      if (wave_trace<2, SCHED, STATS>(dev, st, a, sc, rows, jobs, sample) != 0) return -1;
+      *launches += 2;
+    }
+    rt_wave_combine_kernel<<<blocks, 256, 0, s>>>(a, st->wave, rows, jobs, sample, st->d_counters);
+    *launches += 1;
+  }
+  return 0;
+}
+
 void rt_destroy(vx_device* dev) {
   if (!dev->rt) return;
   cudaFree(dev->rt->d_counters);
   if (dev->rt->wide.d_nodes4) cudaFree(dev->rt->wide.d_nodes4);
   if (dev->rt->d_spill) cudaFree(dev->rt->d_spill);
   if (dev->rt->d_samples) cudaFree(dev->rt->d_samples);
+  if (dev->rt->d_wave) cudaFree(dev->rt->d_wave);
   delete dev->rt;
   dev->rt = nullptr;
 }
@@ -185,23 +282,44 @@ static int validate(const kernel_arg_t& a) {
   return 0;
 }
 
+// [addr, addr + bytes) must lie inside one live allocation: a short or stale address is refused here (-1, like
+// the other argument checks) instead of faulting inside a kernel, which would poison the CUDA context.
+static bool inside_buffer(vx_device* dev, uint64_t addr, uint64_t bytes) {
+  const vx_buffer* b = find_buffer(dev, addr);
+  return b && addr + bytes <= b->reported_addr + b->size;
+}
+
 int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   RtState* st;
   if (validate(a) != 0) {
     fprintf(stderr, "[VXDRV] raytrace: invalid kernel_arg_t\n");
     return -1;
   }
+  if (a.mode == SRT_MODE_RAYS) {
+    if (a.num_rays && (!inside_buffer(dev, a.ray_addr, a.num_rays * sizeof(srt_ray_t)) ||
+                       !inside_buffer(dev, a.hit_addr, a.num_rays * sizeof(srt_hit_t)))) {
+      fprintf(stderr, "[VXDRV] raytrace: ray_addr / hit_addr do not hold %llu records\n", (unsigned long long)a.num_rays);
+      return -1;
+    }
+  } else {
+    const uint32_t rows_ = srt_rank_rows(a.dst_height, a.rows_per_block, a.num_ranks, a.rank_id);
+    if (rows_ && !inside_buffer(dev, a.cbuf_addr, (uint64_t)(rows_ - 1) * a.cbuf_pitch + (uint64_t)a.dst_width * 4)) {
+      fprintf(stderr, "[VXDRV] raytrace: cbuf_addr does not hold %u rows of pitch %u\n", rows_, a.cbuf_pitch);
+      return -1;
+    }
+  }
   if (rt_state(dev, &st) != 0) return -1;
   cudaStream_t s = dev->stream;
   const bool stats = vx_dev_counting(dev);
   const uint32_t variant = dev->dcrs.count(VX_DCR_RT_VARIANT) ? dev->dcrs[VX_DCR_RT_VARIANT] : 0u;
-  if (variant > 3u) {
+  if (variant > 5u) {
     fprintf(stderr, "[VXDRV] raytrace: unknown kernel variant %u\n", variant);
     return -1;
   }
   const bool wide = variant != 1u;
   const bool pooled = variant == 3u;
-  const int sched = variant == 2u ? SCHED_WHILE : SCHED_VOTE;
+  const bool wave = variant >= 4u;  // 4: wavefront pipeline, while-while trace kernels; 5: vote-scheduled
+  const int sched = (variant == 2u || variant == 4u) ? SCHED_WHILE : SCHED_VOTE;
   dev->last_launches = 0;
   dev->last_node_bytes = wide ? (uint32_t)sizeof(Node4) : 32u;
   if (wide && wide_prepare(dev, st, a) != 0) return -1;
@@ -302,6 +420,21 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   dev->last_rt_stores = (uint64_t)rows * a.dst_width;
   if (rows == 0) return 0;
   const uint32_t tiles = ((a.dst_width + 7) / 8) * ((rows + 3) / 4);  // one 8x4 pixel tile = 32 jobs
+  if (wave) {
+    const uint64_t jobs = (uint64_t)tiles * 32u;
+    if (jobs > 0x7FFFFF00ull) return -1;
+    if (wave_reserve(st, jobs, a.spp > 1) != 0) return -1;
+    uint32_t n = 0;
+    int rc;
+    if (sched == SCHED_WHILE) rc = stats ? wave_frame<SCHED_WHILE, true>(dev, st, a, sc, rows, (uint32_t)jobs, &n)
+                                         : wave_frame<SCHED_WHILE, false>(dev, st, a, sc, rows, (uint32_t)jobs, &n);
+    else rc = stats ? wave_frame<SCHED_VOTE, true>(dev, st, a, sc, rows, (uint32_t)jobs, &n)
+                    : wave_frame<SCHED_VOTE, false>(dev, st, a, sc, rows, (uint32_t)jobs, &n);
+    if (rc != 0) return -1;
+    VX_CUDA_OK(cudaGetLastError());
+    dev->last_launches = n + extra_launches;
+    return 0;
+  }
   if (wide) {
     uint64_t jobs = (uint64_t)tiles * 32u;
     if (jobs > 0xFFFFFF00ull) return -1;

@@ -263,7 +263,7 @@ int repack_bvh4(const srt_bvh2_node_t* n2, uint32_t num_nodes, const srt_tri_rec
     if (collapse4(n2, num_nodes, num_tris, src[w], ch, count) != 0) return -1;
     Node4 nd;
     for (int s = 0; s < 4; ++s) {
-      for (int k = 0; k < 6; ++k) nd.plane[k][s] = 3.0e38f;
+      for (int k = 0; k < 6; ++k) nd.plane[k][s] = (k & 1) ? -INFINITY : INFINITY;
       nd.ref[s] = kEmptyRef;
       nd.pad[s] = 0;
     }

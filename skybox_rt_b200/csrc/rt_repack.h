@@ -29,7 +29,8 @@ static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
 // Child ref: bit 31 clear = index of another Node4; bit 31 set = ONE triangle, bits 0-30 = its record
 // index in the builder's own, unpermuted record array (the child box is then that triangle's box, so
 // the ray/triangle test only runs for triangles whose box the ray enters).
-// Empty slots hold the degenerate box lo = hi = +3e38 that no ray interval can reach.
+// Empty slots hold the inverted box lo = +inf, hi = -inf: entry = +inf > exit = -inf for every direction sign and
+// every [tmin, tmax], tmax = +inf included (1 / d is clamped to a finite value, so no inf * 0).
 struct Node4 {
   float plane[6][4];
   uint32_t ref[4];

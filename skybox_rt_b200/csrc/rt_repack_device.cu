@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(128) repack_emit_kernel(const srt_bvh2_node_t*
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
 #pragma unroll
-    for (int k = 0; k < 6; ++k) plane[k][s] = 3.0e38f;
+    for (int k = 0; k < 6; ++k) plane[k][s] = (k & 1) ? -__int_as_float(0x7f800000) : __int_as_float(0x7f800000);
     ref[s] = kEmptyRef;
   }
   uint32_t next = next_begin + offset[i].x;

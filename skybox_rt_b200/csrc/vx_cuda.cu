@@ -51,6 +51,7 @@ void unlink_buffer(vx_buffer* b) {
 // the kernels and copies already queued, so vx_mem_free does not have to wait for them.  The per-draw
 // alloc / upload / free pattern of the reference's apps (draw3d/main.cpp:198-211, :346) costs microseconds.
 int destroy_buffer(vx_buffer* b) {
+  srt::rt_buffer_freed(b->dev, b);
   unlink_buffer(b);
   cudaError_t e = cudaFreeAsync(b->dptr, b->dev->stream);
   free(b->shadow);
@@ -71,6 +72,7 @@ int alloc_buffer(vx_device* dev, uint64_t size, int flags, uint64_t reported, vx
   b->flags = flags;
   b->shadow = size <= kShadowMaxBytes ? (uint8_t*)calloc(1, size) : nullptr;
   b->generation = 0;
+  b->uid = ++dev->next_uid;
   b->prev = nullptr;
   b->next = dev->buffers;
   if (dev->buffers) dev->buffers->prev = b;
@@ -98,6 +100,7 @@ int vx_dev_open(vx_device_h* hdevice) {
   if (!dev) return -1;
   dev->cuda_dev = ordinal;
   dev->buffers = nullptr;
+  dev->next_uid = 0;
   dev->bytes_used = 0;
   dev->rt = nullptr;
   dev->raster = nullptr;
@@ -316,6 +319,28 @@ int vx_start(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments) {
     fprintf(stderr, "[VXDRV] vx_start: bad kernel magic (RISC-V .vxbin images cannot run on the CUDA back-end)\n");
     return -1;
   }
+  // decode the arguments before any run state is touched: a refused launch leaves the previous run's record intact
+  kernel_arg_t rt_arg;
+  draw3d_kernel_arg_t d3_arg;
+  switch (img.pipeline) {
+    case SRT_PIPELINE_RAYTRACE:
+      if (!args->shadow || args->size < sizeof(rt_arg)) {
+        fprintf(stderr, "[VXDRV] vx_start: arguments buffer too small for kernel_arg_t\n");
+        return -1;
+      }
+      memcpy(&rt_arg, args->shadow, sizeof(rt_arg));
+      break;
+    case SRT_PIPELINE_DRAW3D:
+      if (!args->shadow || args->size < sizeof(d3_arg)) {
+        fprintf(stderr, "[VXDRV] vx_start: arguments buffer too small for the draw3d kernel_arg_t\n");
+        return -1;
+      }
+      memcpy(&d3_arg, args->shadow, sizeof(d3_arg));
+      break;
+    default:
+      fprintf(stderr, "[VXDRV] vx_start: unknown pipeline %u\n", img.pipeline);
+      return -1;
+  }
   VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
   // VORTEX_PROFILING=<class> turns the performance monitor on for every run (stub/vortex.cpp:142-149)
   static const int profiling_mode = env_int("VORTEX_PROFILING", 0);
@@ -324,38 +349,20 @@ int vx_start(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments) {
   if (dev->run_mpm_class != 0 && harvest(dev) != 0) return -1;
   dev->run_mpm_class = (int)vx_dev_dcr(dev, VX_DCR_BASE_MPM_CLASS);
   dev->harvested = false;
-  VX_CUDA_OK(cudaEventRecord(dev->ev_start, dev->stream));
-  int rc = -1;
+  dev->run_recorded = false;
   dev->last_counters_valid = false;
   dev->last_pipeline = (int)img.pipeline;
-  switch (img.pipeline) {
-    case SRT_PIPELINE_RAYTRACE: {
-      kernel_arg_t a;
-      if (!args->shadow || args->size < sizeof(a)) {
-        fprintf(stderr, "[VXDRV] vx_start: arguments buffer too small for kernel_arg_t\n");
-        return -1;
-      }
-      memcpy(&a, args->shadow, sizeof(a));
-      rc = srt::rt_launch(dev, a);
-      break;
-    }
-    case SRT_PIPELINE_DRAW3D: {
-      draw3d_kernel_arg_t a;
-      if (!args->shadow || args->size < sizeof(a)) {
-        fprintf(stderr, "[VXDRV] vx_start: arguments buffer too small for the draw3d kernel_arg_t\n");
-        return -1;
-      }
-      memcpy(&a, args->shadow, sizeof(a));
-      rc = srt::raster_launch(dev, a);
-      break;
-    }
-    default:
-      fprintf(stderr, "[VXDRV] vx_start: unknown pipeline %u\n", img.pipeline);
-      return -1;
+  VX_CUDA_OK(cudaEventRecord(dev->ev_start, dev->stream));
+  const int rc = img.pipeline == SRT_PIPELINE_RAYTRACE ? srt::rt_launch(dev, rt_arg) : srt::raster_launch(dev, d3_arg);
+  if (rc != 0) {
+    // nothing was enqueued (the launch functions validate before they launch): there is no run to harvest
+    dev->harvested = true;
+    dev->run_mpm_class = 0;
+    return rc;
   }
   VX_CUDA_OK(cudaEventRecord(dev->ev_stop, dev->stream));
-  dev->run_recorded = (rc == 0);
-  return rc;
+  dev->run_recorded = true;
+  return 0;
 }
 
 int vx_ready_wait(vx_device_h hdevice, uint64_t timeout) {
@@ -532,6 +539,46 @@ int vx_cuda_fill32(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, uint32_t
     for (uint64_t i = 0; i < size / 4; ++i) memcpy(b->shadow + offset + 4 * i, &value, 4);
   }
   return 0;
+}
+
+namespace {
+__global__ void __launch_bounds__(256) probe_read_kernel(const uint4* __restrict__ src, uint64_t n16, uint32_t* sink) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  uint32_t acc = 0;
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n16; i += 4 * stride) {  // four independent 16-byte loads in flight per thread
+    const uint4 a = __ldg(src + i), b = __ldg(src + i + stride), c = __ldg(src + i + 2 * stride), d = __ldg(src + i + 3 * stride);
+    acc ^= a.x ^ a.y ^ a.z ^ a.w ^ b.x ^ b.y ^ b.z ^ b.w ^ c.x ^ c.y ^ c.z ^ c.w ^ d.x ^ d.y ^ d.z ^ d.w;
+  }
+  for (; i < n16; i += stride) { const uint4 a = __ldg(src + i); acc ^= a.x ^ a.y ^ a.z ^ a.w; }
+  if (acc == 0x9e3779b9u) *sink = acc;  // keeps the loads alive; the buffer is zero-filled, so never taken
+}
+}  // namespace
+
+int vx_cuda_probe_read_bandwidth(vx_device_h hdevice, uint64_t bytes, uint32_t repeats, float* ms) {
+  if (nullptr == hdevice || nullptr == ms || bytes < 16 || (bytes & 15) || repeats == 0) return -1;
+  vx_device* dev = as_dev(hdevice);
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  uint4* buf = nullptr;
+  uint32_t* sink = nullptr;
+  cudaEvent_t e0, e1;
+  VX_CUDA_OK(cudaMalloc(&buf, bytes + 16));
+  sink = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(buf) + bytes);
+  int rc = -1;
+  if (cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess) {
+    const unsigned grid = (unsigned)dev->prop.multiProcessorCount * 8u;
+    cudaMemsetAsync(buf, 0, bytes + 16, dev->stream);
+    probe_read_kernel<<<grid, 256, 0, dev->stream>>>(buf, bytes / 16, sink);
+    cudaEventRecord(e0, dev->stream);
+    for (uint32_t r = 0; r < repeats; ++r) probe_read_kernel<<<grid, 256, 0, dev->stream>>>(buf, bytes / 16, sink);
+    cudaEventRecord(e1, dev->stream);
+    if (cudaStreamSynchronize(dev->stream) == cudaSuccess && cudaEventElapsedTime(ms, e0, e1) == cudaSuccess) rc = 0;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+  }
+  cudaFree(buf);
+  cudaGetLastError();
+  return rc;
 }
 
 int vx_cuda_host_register(vx_device_h hdevice, void* ptr, uint64_t size) {

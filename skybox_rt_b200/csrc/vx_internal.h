@@ -26,6 +26,7 @@ struct vx_buffer {
   int flags;
   uint8_t* shadow;        // host copy of small host-written buffers (kernel args, kernel images)
   uint64_t generation;    // bumped by every vx_copy_to_dev (invalidates derived device data)
+  uint64_t uid;           // device-wide allocation number, never reused (the pool does reuse addresses)
   vx_buffer* prev;
   vx_buffer* next;
 };
@@ -60,6 +61,7 @@ struct vx_device {
   bool run_recorded;            // ev_start/ev_stop bracket the last vx_start
   std::map<uint32_t, uint32_t> dcrs;
   vx_buffer* buffers;           // intrusive list of live allocations
+  uint64_t next_uid;            // uid of the next allocation
   uint64_t bytes_used;
   srt::RtState* rt;
   // results of the last run, filled lazily by vx_mpm_query / vx_dump_perf
@@ -111,6 +113,7 @@ namespace srt {
 int rt_launch(vx_device* dev, const kernel_arg_t& arg);
 void rt_destroy(vx_device* dev);
 int rt_read_counters(vx_device* dev);
+void rt_buffer_freed(vx_device* dev, const vx_buffer* b);  // drops derived data (Node4 image) built from b
 // raster_pipeline.cu
 int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg);
 int raster_read_counters(vx_device* dev);

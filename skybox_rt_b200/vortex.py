@@ -33,6 +33,9 @@ VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE, VX_DCR_RT_PREFETCH = 
 VX_DCR_RT_REPACK = 0x808  # 0 = BVH2 -> Node4 on the device, 1 = on the host (A/B)
 VX_DCR_RT_SPLIT_SAMPLES = 0x807  # 0 = (pixel, sample) jobs when spp > 1, 1 = never, 2 = always
 RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL = 0, 1, 2, 3
+RT_VARIANT_WAVE, RT_VARIANT_WAVE_VOTE = 4, 5  # wavefront pipeline: trace kernels + shading passes (csrc/rt_wave.cuh)
+RT_VARIANTS = (RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL, RT_VARIANT_WAVE,
+               RT_VARIANT_WAVE_VOTE)  # every shipped kernel variant
 
 EXPORTS = [
     "vx_dev_open", "vx_dev_close", "vx_dev_caps", "vx_mem_alloc", "vx_mem_reserve", "vx_mem_free",
@@ -43,7 +46,7 @@ EXPORTS = [
 ]
 CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx_cuda_host_unregister",
                 "vx_cuda_perf_totals", "vx_cuda_draw3d_binning", "vx_cuda_rt_build_lbvh",
-                "vx_cuda_rt_node4_image", "vx_cuda_fill32"]  # include/vortex_cuda.h
+                "vx_cuda_rt_node4_image", "vx_cuda_fill32", "vx_cuda_probe_read_bandwidth"]  # include/vortex_cuda.h
 
 _lib = None
 
@@ -83,6 +86,7 @@ def lib():
             "vx_cuda_rt_build_lbvh": [vp, vp, u32, C.POINTER(vp), C.POINTER(vp), vp],
             "vx_cuda_rt_node4_image": [vp, vp, u64, C.POINTER(u64)],
             "vx_cuda_fill32": [vp, u64, u64, u32],
+            "vx_cuda_probe_read_bandwidth": [vp, u64, u32, C.POINTER(C.c_float)],
             "vx_cuda_draw3d_binning": [vp, vp, u32, vp, u32, C.c_float, C.c_float, u32, u32, u32, u32, u32, u32,
                                        C.POINTER(vp), C.POINTER(vp), vp],
         }
@@ -215,6 +219,12 @@ class Device:
         out = (C.c_uint64 * 32)()
         _check(lib().vx_cuda_perf_totals(self.handle, out, 32), "vx_cuda_perf_totals")
         return list(out)
+
+    def read_bandwidth_gbs(self, nbytes, repeats=20):
+        """GB/s of the read probe over a private buffer of nbytes (vx_cuda_probe_read_bandwidth)."""
+        ms = C.c_float()
+        _check(lib().vx_cuda_probe_read_bandwidth(self.handle, nbytes, repeats, C.byref(ms)), "vx_cuda_probe_read_bandwidth")
+        return nbytes * repeats / (ms.value * 1e-3) / 1e9
 
     def cuda_stream(self):
         """cudaStream_t (as int) that vx_start launches on -- wrap with torch.cuda.ExternalStream."""

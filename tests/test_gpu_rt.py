@@ -14,7 +14,7 @@ from skybox_rt_b200.formats import HIT, MISS, RAY
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-VARIANTS = [vx.RT_VARIANT_DEFAULT, vx.RT_VARIANT_BASELINE, vx.RT_VARIANT_WHILE, vx.RT_VARIANT_POOL]
+VARIANTS = sorted(vx.RT_VARIANTS)
 
 
 @pytest.fixture(scope="module")
