@@ -66,6 +66,7 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = N x the pixels of the same view (per-GPU work fixed), strong = the same frame split N ways")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-variants", action="store_true", help="skip the untimed A/B steps of the other kernel variants")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
     ap.add_argument("--keep-active", type=int, default=0, help="diagnostic: refill threshold DCR (0 = default)")
     ap.add_argument("--prefetch", type=int, default=0, help="diagnostic: VX_DCR_RT_PREFETCH (2 = no L2 warm-up)")
@@ -127,14 +128,112 @@ def weak_frame(w0, h0, n):
     return w, h
 
 
-def ncu_traffic(args):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the frame's kernel from the committed `ncu --set full`
-    capture of this same configuration (profiles/r01_tri_vote_summary.txt: 64.78 + 6.86 MB); None for any
-    configuration that was not captured."""
-    if args.workload == "c3" and args.variant == 0 and args.gpus == 1 and args.builder == "host" and \
-            args.spp is None and args.mode is None:
-        return 71634432
-    return None
+def profile_inputs(args, wl_key):
+    """Counters read from the committed ncu captures: profiles/roofline_inputs.json maps "<workload>:v<variant>" to
+    {source, issue_active, lanes_per_inst, dram_bytes} (written by profiles/make_roofline_inputs.py from the named
+    summary files).  None for any configuration that was not captured -- nothing is assumed to carry over."""
+    if args.gpus != 1 or args.builder != "host" or args.spp is not None or args.mode is not None:
+        return None
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_inputs.json")) as f:
+            return json.load(f).get(f"{wl_key}:v{args.variant}")
+    except (OSError, ValueError):
+        return None
+
+
+def roofline_record(args, wl, r, dev, tracer, vx, cpu):
+    """Roofline of the frame's traversal work.
+    Algorithmic bytes = the ORACLE's per-ray visit counts on the identical (sub)sample x the oracle's record sizes
+    (BVH2 node 32 B, triangle record 48 B), scaled to the rays of the step, + the framebuffer / ray I/O.  The bound is
+    chosen by working set: a scene that fits the L2 is measured against the L2 -> SM read bandwidth probed on this
+    box (vx_cuda_probe_read_bandwidth), an HBM-resident one against MEASURED_PEAKS.json; the issue roofline
+    (148 SM x 4 schedulers x SM clock) is reported next to it with the counters of the committed capture."""
+    peak_hbm, peak_src = load_peaks()
+    # the kernels' own counts, from an extra untimed step of the counting instantiations
+    dev.dcr_write(vx.VX_DCR_RT_STATS, 1)
+    dev.start(tracer.kernel, tracer.args)
+    dev.ready_wait()
+    st = tracer.counters()
+    wn, wt = dev.mpm_query(vx.VX_CSR_RT_WARP_NODE_STEPS), dev.mpm_query(vx.VX_CSR_RT_WARP_TRI_STEPS)
+    dev.dcr_write(vx.VX_DCR_RT_STATS, 0)
+    node_bytes = dev.mpm_query(vx.VX_CSR_RT_NODE_BYTES)
+    world = r["world"]
+    rays_rank = r["rays_total"] / world
+    fb_bytes = 0 if wl["mode"] == 3 else wl["w"] * wl["h"] * 4 // world
+    ray_io = rays_rank * 48 if wl["mode"] == 3 else 0
+    kernel_bytes = st["nodes"] * node_bytes + st["tris"] * 48 + fb_bytes + ray_io
+    kern_s = r["kern_ms"] * 1e-3
+    rec = {"kernel": "whole vx_start pipeline (trace + shade)", "kernel_ms": r["kern_ms"], "unit": "GB/s",
+           "kernel_counts": {"nodes_fetched": st["nodes"], "node_bytes": int(node_bytes), "tris_tested": st["tris"],
+                             "bytes": int(kernel_bytes),
+                             "lanes_per_node_step": round(st["nodes"] / wn, 2) if wn else None,
+                             "lanes_per_tri_step": round(st["tris"] / wt, 2) if wt else None}}
+    if cpu is not None:
+        oc = cpu["counters"]
+        scale = rays_rank / max(1, cpu["rays_per_step"])
+        alg = (oc["nodes_visited"] * 32 + oc["tris_tested"] * 48) * scale + fb_bytes + ray_io
+        rec.update(counts_source="oracle", algorithmic_bytes=int(alg),
+                   oracle_counts={"nodes_visited": oc["nodes_visited"], "tris_tested": oc["tris_tested"],
+                                  "rays": cpu["rays_per_step"], "sample": cpu["sample"], "scaled_by": round(scale, 3),
+                                  "node_bytes": 32})
+    else:
+        alg = kernel_bytes
+        rec.update(counts_source="kernel (no oracle run in this invocation)", algorithmic_bytes=int(alg))
+    achieved = alg / kern_s / 1e9 if kern_s > 0 else 0.0
+    # working set: the wide-node image + triangle records the kernels read
+    ws = r["n_tris"] * 48 + (r["n_nodes"] * 32 if args.variant == vx.RT_VARIANT_BASELINE else dev.node4_image_size())
+    l2_bytes = r["torch"].cuda.get_device_properties(r["torch"].cuda.current_device()).L2_cache_size
+    try:
+        l2_gbs = dev.read_bandwidth_gbs(64 << 20, 20)
+        hbm_gbs = dev.read_bandwidth_gbs(2 << 30, 4)
+    except Exception:  # noqa: BLE001 -- the probe is a report, not the product
+        l2_gbs = hbm_gbs = None
+    resident = ws < 0.8 * l2_bytes
+    if resident and l2_gbs:
+        rec.update(bound="l2", peak=l2_gbs, peak_source="L2 -> SM read bandwidth probed on this box: 64 MiB buffer, "
+                   "16-byte read-only loads, 20 passes (vx_cuda_probe_read_bandwidth)")
+    else:
+        rec.update(bound="hbm", peak=peak_hbm, peak_source=peak_src)
+    rec.update(achieved=achieved, frac=achieved / rec["peak"], hbm_frac=achieved / peak_hbm,
+               l2_frac=achieved / l2_gbs if l2_gbs else None, working_set_bytes=int(ws),
+               probed={"l2_read_gbs": l2_gbs, "hbm_read_gbs": hbm_gbs})
+    sm_mhz = (r["clocks"] or {}).get("sm_mhz") or 1965.0
+    issue_peak = 148 * 4 * sm_mhz * 1e6
+    pi = profile_inputs(args, args.workload)
+    rec["issue"] = {"peak_warp_inst_per_s": issue_peak, "sm_mhz": sm_mhz}
+    if pi:
+        rec["traffic"] = pi.get("dram_bytes")
+        rec["issue"].update(issue_active=pi.get("issue_active"), lanes_per_inst=pi.get("lanes_per_inst"),
+                            warp_inst_per_step=pi.get("warp_inst"), source=pi.get("source"))
+        if pi.get("warp_inst"):
+            rec["issue"]["frac"] = pi["warp_inst"] / kern_s / issue_peak
+    else:
+        rec["traffic"] = None
+    return rec
+
+
+def variants_ms(args, r, dev, tracer, vx):
+    """Device ms per frame of every shipped kernel variant on this workload (3 frames each after one warm-up, L2
+    flushed before each, untimed as far as `value` is concerned): the A/B every optimisation is argued from."""
+    torch, stream, flush = r["torch"], r["stream"], r["flush"]
+    res = {}
+    for v in sorted(vx.RT_VARIANTS):
+        if v == vx.RT_VARIANT_POOL:
+            continue  # explicit ray lists only
+        dev.dcr_write(vx.VX_DCR_RT_VARIANT, v)
+        ts = []
+        for i in range(4):
+            with torch.cuda.stream(stream):
+                if not args.no_flush:
+                    flush.zero_()
+            stream.synchronize()
+            dev.start(tracer.kernel, tracer.args)
+            dev.ready_wait()
+            if i:
+                ts.append(dev.mpm_query(vx.VX_CSR_RT_ELAPSED_NS) * 1e-6)
+        res[str(v)] = round(sum(ts) / len(ts), 4)
+    dev.dcr_write(vx.VX_DCR_RT_VARIANT, args.variant)
+    return res
 
 
 def build_scene(wl, rt):
@@ -156,32 +255,39 @@ def scene_box(soup):
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle on the host cores, on a bounded sample of the workload
 # ------------------------------------------------------------------------------------------------
-def cpu_sample_run(wl, soup, nodes, tris, steps, warmup):
+def cpu_sample_run(wl, soup, nodes, tris, steps, warmup, threads=None, shrink=1):
     """Times the CPU oracle.  Sample = the rows a rank would own if the frame were split over
     `div` ranks (interleaved blocks of 8 rows => representative of the whole frame), or the first
-    1/div of the ray list for c5.  Returns (Mrays/s, description, threads, seconds per step)."""
+    1/div of the ray list for c5; `shrink` makes the sample that many times smaller again (single-thread leg).
+    Returns a dict: Mrays/s, sample description, threads, seconds per step, the oracle's counters, and what it
+    rendered (`fb` + the rank split, or `hits` + the rays) so that the GPU frame can be checked against it."""
     import _oracle as o
-    threads = os.cpu_count() or 1
+    threads = threads or (os.cpu_count() or 1)
+    out = {"threads": threads}
     if wl["mode"] == 3:
-        n = min(wl["rays"], 1 << 20)
+        n = min(wl["rays"], (1 << 20) // shrink)
         lo, hi = scene_box(soup)
         rays = o.rays_random(lo, hi, 0x5EED5EED, 0, n)
 
         def run():
-            _, c = o.trace(rays, nodes, tris, threads=threads, num_tasks=threads * 16)
+            h, c = o.trace(rays, nodes, tris, threads=threads, num_tasks=threads * 16)
+            out["hits"] = h
             return c
+        out["rays_in"] = rays
         sample = f"first {n} of {wl['rays']} rays"
     else:
         paths = wl["w"] * wl["h"] * wl["spp"]
         div = 1
-        while paths // div > 300_000 and div < 64:
+        while paths // div > 300_000 // shrink and div < 256:
             div *= 2
         a = o.make_arg(wl["w"], wl["h"], wl["mode"], spp=wl["spp"], seed=1234, scene=wl["scene"],
                        num_tasks=wl["h"])
         a.num_ranks, a.rank_id, a.rows_per_block = div, 0, ROWS_PER_BLOCK
+        out["div"] = div
 
         def run():
-            _, c = o.render(a, nodes, tris, threads=threads)
+            fb, c = o.render(a, nodes, tris, threads=threads)
+            out["fb"] = fb
             return c
         sample = (f"rows of rank 0 of {div} (interleaved blocks of {ROWS_PER_BLOCK} rows) of the "
                   f"{wl['w']}x{wl['h']}x{wl['spp']}spp frame" if div > 1 else "the whole frame")
@@ -193,7 +299,30 @@ def cpu_sample_run(wl, soup, nodes, tris, steps, warmup):
         c = run()
         rays_total += c["rays_primary"] + c["rays_shadow"] + c["rays_bounce"]
     dt = time.perf_counter() - t0
-    return rays_total / dt / 1e6, sample, threads, dt / steps, c
+    out.update(value=rays_total / dt / 1e6, sample=sample, sec_per_step=dt / steps, counters=c,
+               rays_per_step=rays_total // steps)
+    return out
+
+
+def parity_check(wl, tracer, cpu):
+    """The frame the bench times against what the oracle just rendered: the GPU renders the same rows (same rank
+    split, same seed) once, untimed, and every pixel and ray counter must match bit for bit; for c5 the first hit
+    records are compared as raw bytes.  (tests/regression/draw3d/main.cpp:505-514: compare what you rendered.)"""
+    from skybox_rt_b200 import raytrace as rt
+    if wl["mode"] == 3:
+        hits = tracer.trace(cpu["rays_in"])
+        ref = cpu["hits"]
+        bad = int((hits.view(np.uint8).reshape(len(hits), -1) != ref.view(np.uint8).reshape(len(ref), -1)).any(axis=1).sum())
+        return {"rays": int(len(ref)), "mismatches": bad, "against": "oracle hit records, raw bytes"}
+    a = rt.make_arg(wl["w"], wl["h"], wl["mode"], spp=wl["spp"], seed=1234, scene=wl["scene"], rank=0,
+                    num_ranks=cpu["div"], rows_per_block=ROWS_PER_BLOCK)
+    fb = tracer.render(a).copy()
+    c = tracer.counters()
+    ref, oc = cpu["fb"], cpu["counters"]
+    bad = int((fb != ref).sum()) if fb.shape == ref.shape else int(ref.size)
+    counters_equal = all(c[k] == oc[k] for k in ("rays_primary", "rays_shadow", "rays_bounce"))
+    return {"rows": int(ref.shape[0]), "pixels": int(ref.size), "mismatches": bad, "ray_counters_equal": counters_equal,
+            "against": f"oracle frame, rank 0 of {cpu['div']}, A8R8G8B8 words"}
 
 
 def reference_arm(args, wl):
@@ -203,13 +332,17 @@ def reference_arm(args, wl):
     from skybox_rt_b200 import raytrace as rt  # host pre-pass only (plain C, no CUDA)
     soup, nodes, tris, _ = build_scene(wl, rt)
     steps, warmup = max(1, args.steps), max(0, args.warmup)
-    v, sample, threads, sec, _ = cpu_sample_run(wl, soup, nodes, tris, steps, warmup)
+    r = cpu_sample_run(wl, soup, nodes, tris, steps, warmup)
+    v = r["value"]
     print(json.dumps({
         "impl": "reference", "metric": "Mrays/s (primary+shadow+bounce rays traced)", "value": v, "unit": "Mrays/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3,
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["sec_per_step"] * 1e3,
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["name"]},
-        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": r["threads"], "kind": "port", "sample": r["sample"],
+                         "tree": "binned-SAH BVH2 from this repo's host builder (libskybox_rt_host.so), the one the GPU "
+                                 "arm uploads: a better tree than the oracle's own spatial-median builder, so this arm "
+                                 "is not understated"},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference repo has no RT path (SURVEY.md section 0); this is the repo's plain-C oracle",
     }))
@@ -393,7 +526,8 @@ def native_arm(args, wl):
         rays_total, kern_ms = float(rays_per_step), kern_ns * 1e-6
     return dict(rank=rank, world=world, dev_ms=dev_ms, e2e_s=e2e_s, rays_total=rays_total, kern_ms=kern_ms,
                 clocks=clocks, h2d=h2d, d2h=d2h, ctr=ctr, build_s=build_s, device_build_ms=device_build_ms, t_wall=t_wall, soup=soup, nodes=nodes,
-                tris=tris, tracer=tracer, n_nodes=len(nodes), n_tris=len(tris))
+                tris=tris, tracer=tracer, n_nodes=len(nodes), n_tris=len(tris), stream=stream, flush=flush, launch=launch,
+                torch=torch)
 
 
 def load_peaks():
@@ -439,19 +573,6 @@ def main():
         ms_per_step = r["dev_ms"] / K
         value = r["rays_total"] / (ms_per_step * 1e-3) / 1e6
         e2e = r["rays_total"] / (r["e2e_s"] / K) / 1e6
-        peak, peak_src = load_peaks()
-        # algorithmic bytes of the traversal: nodes fetched x node size + triangles tested x 48 B
-        # (counted by the kernels themselves in an extra, untimed step with VX_DCR_RT_STATS = 1)
-        dev.dcr_write(vx.VX_DCR_RT_STATS, 1)
-        dev.start(tracer.kernel, tracer.args)
-        dev.ready_wait()
-        st = tracer.counters()
-        dev.dcr_write(vx.VX_DCR_RT_STATS, 0)
-        node_bytes = dev.mpm_query(vx.VX_CSR_RT_NODE_BYTES)
-        fb_bytes = 0 if wl["mode"] == 3 else wl["w"] * wl["h"] * 4 // r["world"]
-        ray_io = (r["rays_total"] / r["world"]) * 48 if wl["mode"] == 3 else 0
-        alg_bytes = st["nodes"] * node_bytes + st["tris"] * 48 + fb_bytes + ray_io
-        achieved = alg_bytes / (r["kern_ms"] * 1e-3) / 1e9 if r["kern_ms"] > 0 else 0.0
         out = {
             "metric": "Mrays/s (primary+shadow+bounce rays traced)", "value": value, "unit": "Mrays/s",
             "n_gpus": r["world"], "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
@@ -467,20 +588,20 @@ def main():
                     "ms_per_step": r["e2e_s"] / K * 1e3},
             "gpu_launches": int(dev.mpm_query(vx.VX_CSR_RT_LAUNCHES)) * K,
             "clocks": r["clocks"],
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": ncu_traffic(args), "peak_source": peak_src,
-                         "kernel": "whole vx_start pipeline (trace + shade)", "kernel_ms": r["kern_ms"],
-                         "algorithmic_bytes": int(alg_bytes), "nodes_fetched": st["nodes"],
-                         "node_bytes": int(node_bytes), "tris_tested": st["tris"],
-                         "note": "algorithmic bytes are mostly served by L1/L2 (the C3 scene is L2-resident): the kernel is "
-                                 "bound by issue slots x lanes per instruction, not by HBM -- ncu: 66 % issue-active at "
-                                 "14.2 of 32 lanes (profiles/r01_tri_vote_summary.txt, DESIGN.md section 4)"},
             "host_prepass_s": {"bvh2_build": r["build_s"]},
             "builder": args.builder, "device_open_upload_build_ms": r.get("device_build_ms"),
         }
+        cpu = None
         if r["world"] == 1 and not args.no_cpu_baseline:
-            v, sample, threads, _, _ = cpu_sample_run(wl, r["soup"], r["nodes"], r["tris"], steps=3, warmup=1)
-            out["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample}
+            cpu = cpu_sample_run(wl, r["soup"], r["nodes"], r["tris"], steps=3, warmup=1)
+            one = cpu_sample_run(wl, r["soup"], r["nodes"], r["tris"], steps=1, warmup=0, threads=1, shrink=8)
+            out["cpu_baseline"] = {"value": cpu["value"], "unit": "Mrays/s", "cores": cpu["threads"], "kind": "port",
+                                   "sample": cpu["sample"],
+                                   "single_thread": {"value": one["value"], "unit": "Mrays/s", "cores": 1, "sample": one["sample"]}}
+            out["parity_check"] = parity_check(wl, tracer, cpu)
+        out["roofline"] = roofline_record(args, wl, r, dev, tracer, vx, cpu)
+        if r["world"] == 1 and wl["mode"] != 3 and not args.no_variants:
+            out["variants_ms"] = variants_ms(args, r, dev, tracer, vx)
     tracer.close()
     if r["world"] > 1:
         import torch.distributed as dist
@@ -488,6 +609,9 @@ def main():
         dist.destroy_process_group()
     if out is not None:
         print(json.dumps(out))
+        pc = out.get("parity_check")
+        if pc and (pc["mismatches"] != 0 or pc.get("ray_counters_equal") is False):
+            sys.exit(f"bench.py: the timed frame differs from the oracle: {pc}")
 
 
 if __name__ == "__main__":

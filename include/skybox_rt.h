@@ -171,6 +171,8 @@ typedef struct {
 #define VX_CSR_RT_ELAPSED_NS   0x7C5 /* device time of the last run, CUDA events             */
 #define VX_CSR_RT_NODE_BYTES   0x7C6 /* bytes per node fetch of the kernel variant that ran  */
 #define VX_CSR_RT_LAUNCHES     0x7C7 /* kernels launched by the last vx_start                */
+#define VX_CSR_RT_WARP_NODE_STEPS 0x7C8 /* warp-level node steps (STATS): NODES / this = lanes per node step */
+#define VX_CSR_RT_WARP_TRI_STEPS  0x7C9 /* warp-level triangle steps (STATS)                                  */
 
 /* ------------------------------------------------------------------------------------
  * Performance monitor, reference numbering (hw/rtl/VX_types.vh:27, :35-40, :66-247).

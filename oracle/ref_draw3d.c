@@ -902,6 +902,11 @@ static uint32_t to_vx_blend_func(uint32_t o) {
 
 /* main.cpp:214-346: the DCR writes and the boolean switches of one draw call.  `arg` persists across
  * draws (the reference's global kernel_arg), so state a draw does not write keeps its last value. */
+/* Test hook (not in main.cpp, which always programs MODE_ADD): OM DCR values for draws whose trace state enables
+ * blending -- blend mode, blend func, blend constant, logic op (same hook as oracle/ref_draw3d_harness.cpp). */
+static uint32_t g_om_override[4];
+static int g_om_override_on = 0;
+
 static void program_draw(draw3d_kernel_arg_t* arg, const srt_states_t* st, const o_tex_t* tex, uint32_t num_tiles,
                          uint32_t width, uint32_t height) {
   RAS(arg, VX_DCR_RASTER_TILE_COUNT) = num_tiles;
@@ -935,7 +940,12 @@ static void program_draw(draw3d_kernel_arg_t* arg, const srt_states_t* st, const
     OM(arg, VX_DCR_OM_STENCIL_WRITEMASK) = 0;
   }
   OM(arg, VX_DCR_OM_BLEND_MODE) = (VX_OM_BLEND_MODE_ADD << 16) | (VX_OM_BLEND_MODE_ADD << 0);
-  if (st->blend_enabled) {
+  if (st->blend_enabled && g_om_override_on) { /* test hook, not in main.cpp (see ord_set_om_override) */
+    OM(arg, VX_DCR_OM_BLEND_MODE) = g_om_override[0];
+    OM(arg, VX_DCR_OM_BLEND_FUNC) = g_om_override[1];
+    OM(arg, VX_DCR_OM_BLEND_CONST) = g_om_override[2];
+    OM(arg, VX_DCR_OM_LOGIC_OP) = g_om_override[3];
+  } else if (st->blend_enabled) {
     uint32_t s = to_vx_blend_func(st->blend_src), d = to_vx_blend_func(st->blend_dst);
     OM(arg, VX_DCR_OM_BLEND_FUNC) = (d << 24) | (d << 16) | (s << 8) | (s << 0);
   } else {
@@ -964,6 +974,12 @@ static double now_s(void) {
   struct timespec t;
   clock_gettime(CLOCK_MONOTONIC, &t);
   return (double)t.tv_sec + 1e-9 * (double)t.tv_nsec;
+}
+
+void ref_draw3d_set_om_override(const uint32_t* ov) {
+  int i;
+  g_om_override_on = ov != 0;
+  if (ov) for (i = 0; i < 4; ++i) g_om_override[i] = ov[i];
 }
 
 uint32_t ref_draw3d_kernel_arg_size(void) { return (uint32_t)sizeof(draw3d_kernel_arg_t); }

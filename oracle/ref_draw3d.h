@@ -40,6 +40,9 @@ int64_t ref_draw3d_binning(const uint8_t* blob, uint64_t blob_size, uint32_t dra
 
 uint64_t ref_draw3d_count_fragments(const uint8_t* blob, uint64_t blob_size, uint32_t width, uint32_t height,
                                     uint32_t num_threads);
+/* Test hook: OM DCR values {blend mode, blend func, blend constant, logic op} programmed for every draw whose trace
+ * state enables blending (the reference app itself only ever programs MODE_ADD, main.cpp:271-279); NULL clears it. */
+void ref_draw3d_set_om_override(const uint32_t* ov);
 uint32_t ref_draw3d_kernel_arg_size(void);
 uint32_t ref_draw3d_prim_size(void);
 

@@ -184,6 +184,15 @@ int64_t ref_draw3d_binning(const uint8_t* blob, uint64_t blob_size, uint32_t dra
   return n;
 }
 
+// Test hook (no counterpart in main.cpp, which always programs MODE_ADD): the four OM DCR values used for every
+// draw whose trace state enables blending -- blend mode, blend func, blend constant, logic op.  ov == NULL clears it.
+static uint32_t g_om_override[4];
+static bool g_om_override_on = false;
+void ref_draw3d_set_om_override(const uint32_t* ov) {
+  g_om_override_on = ov != nullptr;
+  if (ov) for (int i = 0; i < 4; ++i) g_om_override[i] = ov[i];
+}
+
 // Whole-trace render, the flow of draw3d/main.cpp:392-517 + render() :171-389 with -x -y -u.
 // cbuf_out / zbuf_out: width*height u32, row 0 = framebuffer row 0 (the saved PNG is this flipped).
 // kernel_seconds (optional) = time inside the kernel launches only (main.cpp:349-361 measures the same span).
@@ -268,7 +277,12 @@ int ref_draw3d_render(const uint8_t* blob, uint64_t blob_size, uint32_t dst_widt
       OM_DCR_WRITE(VX_DCR_OM_STENCIL_MASK, VX_OM_STENCIL_MASK);
       OM_DCR_WRITE(VX_DCR_OM_STENCIL_WRITEMASK, 0);
     }
-    if (states.blend_enabled) {
+    if (states.blend_enabled && g_om_override_on) {  // not in main.cpp: OM state the trace format cannot express
+      OM_DCR_WRITE(VX_DCR_OM_BLEND_MODE, g_om_override[0]);
+      OM_DCR_WRITE(VX_DCR_OM_BLEND_FUNC, g_om_override[1]);
+      OM_DCR_WRITE(VX_DCR_OM_BLEND_CONST, g_om_override[2]);
+      OM_DCR_WRITE(VX_DCR_OM_LOGIC_OP, g_om_override[3]);
+    } else if (states.blend_enabled) {
       auto blend_src = graphics::toVXBlendFunc(states.blend_src);
       auto blend_dst = graphics::toVXBlendFunc(states.blend_dst);
       OM_DCR_WRITE(VX_DCR_OM_BLEND_MODE, (VX_OM_BLEND_MODE_ADD << 16) | (VX_OM_BLEND_MODE_ADD << 0));

@@ -45,6 +45,8 @@ struct srt_draw3d {
   uint32_t *clear_z, *clear_c;
   int clear_z_pinned, clear_c_pinned;
   srt_draw3d_stats_t stats;
+  srt_om_override_t om_override;
+  int om_override_on;
 };
 
 static double now_ms(void) {
@@ -153,7 +155,12 @@ static int program_draw(srt_draw3d_t* r, draw3d_kernel_arg_t* arg, int live, con
     om_w(&c, VX_DCR_OM_STENCIL_WRITEMASK, 0);
   }
   om_w(&c, VX_DCR_OM_BLEND_MODE, (VX_OM_BLEND_MODE_ADD << 16) | (VX_OM_BLEND_MODE_ADD << 0));
-  if (st->blend_enabled) {
+  if (st->blend_enabled && r->om_override_on) { /* state beyond the trace format (srt_draw3d_set_om_override) */
+    om_w(&c, VX_DCR_OM_BLEND_MODE, r->om_override.blend_mode);
+    om_w(&c, VX_DCR_OM_BLEND_FUNC, r->om_override.blend_func);
+    om_w(&c, VX_DCR_OM_BLEND_CONST, r->om_override.blend_const);
+    om_w(&c, VX_DCR_OM_LOGIC_OP, r->om_override.logic_op);
+  } else if (st->blend_enabled) {
     if (to_vx_blend_func(st->blend_src, &v0) || to_vx_blend_func(st->blend_dst, &v1)) return -1;
     om_w(&c, VX_DCR_OM_BLEND_FUNC, (v1 << 24) | (v1 << 16) | (v0 << 8) | (v0 << 0));
   } else {
@@ -252,6 +259,12 @@ static void free_slots(srt_draw3d_t* r) {
   free(r->slots);
   r->slots = NULL;
   r->num_slots = 0;
+}
+
+void srt_draw3d_set_om_override(srt_draw3d_t* r, const srt_om_override_t* ov) {
+  if (!r) return;
+  r->om_override_on = ov != NULL;
+  if (ov) r->om_override = *ov;
 }
 
 void srt_draw3d_close(srt_draw3d_t* r) { /* cleanup(), main.cpp:137-146 (the device stays the caller's) */

@@ -48,6 +48,19 @@ int srt_draw3d_open(vx_device_h device, uint32_t width, uint32_t height, uint32_
                     uint32_t num_ranks, srt_draw3d_t** out);
 void srt_draw3d_close(srt_draw3d_t* r);
 
+/* Output-merger state the trace format cannot express.  A .cgltrace carries GL blend factors only, and the reference
+ * app always programs VX_OM_BLEND_MODE_ADD with no logic op and no blend constant (main.cpp:271-279), although its
+ * output merger implements six equations, sixteen logic ops and four CONST_* factors (sim/common/graphics.cpp:366-524).
+ * With an override set, every draw whose trace state enables blending is programmed with these four DCR values
+ * instead (VX_DCR_OM_BLEND_MODE / _FUNC / _CONST / VX_DCR_OM_LOGIC_OP, hw/rtl/VX_types.vh:439-458).  NULL clears it. */
+typedef struct {
+  uint32_t blend_mode;  /* mode_a << 16 | mode_rgb                       */
+  uint32_t blend_func;  /* dst_a << 24 | dst_rgb << 16 | src_a << 8 | src_rgb */
+  uint32_t blend_const; /* A8R8G8B8                                       */
+  uint32_t logic_op;
+} srt_om_override_t;
+void srt_draw3d_set_om_override(srt_draw3d_t* r, const srt_om_override_t* ov);
+
 /* Host upload of the clear values 0xff000000 / 0xffffffff (main.cpp:45-46, :478-490). */
 int srt_draw3d_clear(srt_draw3d_t* r);
 

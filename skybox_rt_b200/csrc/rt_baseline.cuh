@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(256) rt_baseline_kernel(const __grid_constant_
   const uint32_t x = (warp % tiles_x) * 8 + (lane & 7);
   const uint32_t ly = (warp / tiles_x) * 4 + (lane >> 3);
   uint32_t n_shadow = 0, n_bounce = 0;
-  Stats st = {0, 0, 0};
+  Stats st = {0, 0, 0, 0, 0};
   if (x < W && ly < local_rows) {
     const uint32_t y = global_row(a, ly);
     const uint32_t pix = y * W + x;
@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(256) rt_baseline_rays_kernel(const __grid_cons
   const float4* nodes = reinterpret_cast<const float4*>(a.node_addr);
   const float4* tris = reinterpret_cast<const float4*>(a.tri_addr);
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  Stats st = {0, 0, 0};
+  Stats st = {0, 0, 0, 0, 0};
   if (i < a.num_rays) {
     const float4* rp = reinterpret_cast<const float4*>(a.ray_addr) + 2 * i;
     const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);

@@ -184,7 +184,11 @@ __device__ __forceinline__ V3 bounce_dir(uint32_t seed_hash, uint32_t pix, uint3
 struct Stats {
   uint32_t nodes, tris;  // node records fetched / triangles tested by this thread
   uint32_t rays;         // rays started by this thread
+  uint32_t wnode, wtri;  // warp-level node / triangle steps this thread led (lowest active lane): nodes / wnode =
+                         // lanes per node step, the execution efficiency of the traversal loop measured in place
 };
+// call inside a (possibly divergent) step: one lane of the active set counts the step for the warp
+__device__ __forceinline__ bool step_leader() { return (threadIdx.x & 31u) == (uint32_t)(__ffs(__activemask()) - 1); }
 
 // Per-thread traversal statistics -> device counters (warp reduce, one atomic per warp).  All 32
 // lanes of the warp must call this.  Counter slots: vx_internal.h CTR_NODES = 2, CTR_TRIS = 3, CTR_PER_SM = 8.
@@ -193,9 +197,12 @@ __device__ __forceinline__ void flush_stats(const S& st, unsigned long long* cou
   const uint32_t n = __reduce_add_sync(0xffffffffu, st.nodes);
   const uint32_t t = __reduce_add_sync(0xffffffffu, st.tris);
   const uint32_t r = __reduce_add_sync(0xffffffffu, st.rays);
+  const uint32_t wn = __reduce_add_sync(0xffffffffu, st.wnode), wt = __reduce_add_sync(0xffffffffu, st.wtri);
   if ((threadIdx.x & 31) == 0) {
     if (n) atomicAdd(counters + 2, (unsigned long long)n);
     if (t) atomicAdd(counters + 3, (unsigned long long)t);
+    if (wn) atomicAdd(counters + 5, (unsigned long long)wn);
+    if (wt) atomicAdd(counters + 6, (unsigned long long)wt);
     uint32_t smid;
     asm("mov.u32 %0, %%smid;" : "=r"(smid));
     if (r) atomicAdd(counters + 8 + (smid & 255u), (unsigned long long)r);

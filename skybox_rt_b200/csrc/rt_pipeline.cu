@@ -37,8 +37,8 @@ struct WideCache {
 struct RtState {
   unsigned long long* d_counters;  // CTR_COUNT u64, zeroed at every launch
   WideCache wide;
-  int wide_blocks_per_sm[8];       // occupancy of the persistent kernels, queried once
-  int wide_split_blocks_per_sm[8]; // same for the (pixel, sample)-job render kernels
+  int wide_blocks_per_sm[12];      // occupancy of the persistent kernels, queried once
+  int wide_split_blocks_per_sm[12];// same for the (pixel, sample)-job render kernels
   int pool_blocks_per_sm[4];
   uint2* d_spill;                  // stack spill area of the pool kernels (rarely touched)
   size_t spill_warps;
@@ -48,7 +48,7 @@ struct RtState {
   char* d_wave;
   uint64_t wave_jobs;
   WaveBufs wave;
-  int wave_blocks_per_sm[12];      // occupancy per (stage, scheduler, stats) instantiation
+  int wave_blocks_per_sm[18];      // occupancy per (stage, scheduler, stats) instantiation
 };
 
 static int rt_state(vx_device* dev, RtState** out) {
@@ -212,7 +212,7 @@ template <int STAGE, int SCHED, bool STATS>
 static int wave_trace(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, uint32_t rows,
                       uint32_t jobs, uint32_t s) {
   const size_t smem = sizeof(uint2) * kSmStack * kWideThreads;
-  int* occ = st->wave_blocks_per_sm + (STAGE * 4 + SCHED * 2 + (STATS ? 1 : 0));
+  int* occ = st->wave_blocks_per_sm + (STAGE * 6 + SCHED * 2 + (STATS ? 1 : 0));
   auto kernel = rt_wave_trace_kernel<STAGE, SCHED, STATS>;
   if (*occ == 0) {
     int n = 0;
@@ -312,14 +312,14 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   cudaStream_t s = dev->stream;
   const bool stats = vx_dev_counting(dev);
   const uint32_t variant = dev->dcrs.count(VX_DCR_RT_VARIANT) ? dev->dcrs[VX_DCR_RT_VARIANT] : 0u;
-  if (variant > 5u) {
+  if (variant > 6u) {
     fprintf(stderr, "[VXDRV] raytrace: unknown kernel variant %u\n", variant);
     return -1;
   }
   const bool wide = variant != 1u;
   const bool pooled = variant == 3u;
-  const bool wave = variant >= 4u;  // 4: wavefront pipeline, while-while trace kernels; 5: vote-scheduled
-  const int sched = (variant == 2u || variant == 4u) ? SCHED_WHILE : SCHED_VOTE;
+  const bool wave = variant >= 4u;  // wavefront pipeline; trace kernels scheduled 4: while-while, 5: vote, 6: vote + deferred triangle
+  const int sched = (variant == 2u || variant == 4u) ? SCHED_WHILE : (variant == 6u ? SCHED_DEFER : SCHED_VOTE);
   dev->last_launches = 0;
   dev->last_node_bytes = wide ? (uint32_t)sizeof(Node4) : 32u;
   if (wide && wide_prepare(dev, st, a) != 0) return -1;
@@ -359,7 +359,13 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
 #define SRT_LAUNCH_WIDE(KERNEL, OCC, JOBS, ...)                                                    \
   do {                                                                                             \
     int g_;                                                                                        \
-    if (sched == SCHED_VOTE && stats) {                                                            \
+    if (sched == SCHED_DEFER && stats) {                                                           \
+      if ((g_ = persistent_grid(dev, OCC, KERNEL<SCHED_DEFER, true>, smem, JOBS)) <= 0) return -1; \
+      KERNEL<SCHED_DEFER, true><<<g_, kWideThreads, smem, s>>>(__VA_ARGS__);                       \
+    } else if (sched == SCHED_DEFER) {                                                             \
+      if ((g_ = persistent_grid(dev, OCC, KERNEL<SCHED_DEFER, false>, smem, JOBS)) <= 0) return -1;\
+      KERNEL<SCHED_DEFER, false><<<g_, kWideThreads, smem, s>>>(__VA_ARGS__);                      \
+    } else if (sched == SCHED_VOTE && stats) {                                                            \
       if ((g_ = persistent_grid(dev, OCC, KERNEL<SCHED_VOTE, true>, smem, JOBS)) <= 0) return -1;  \
       KERNEL<SCHED_VOTE, true><<<g_, kWideThreads, smem, s>>>(__VA_ARGS__);                        \
     } else if (sched == SCHED_VOTE) {                                                              \
@@ -428,6 +434,8 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
     int rc;
     if (sched == SCHED_WHILE) rc = stats ? wave_frame<SCHED_WHILE, true>(dev, st, a, sc, rows, (uint32_t)jobs, &n)
                                          : wave_frame<SCHED_WHILE, false>(dev, st, a, sc, rows, (uint32_t)jobs, &n);
+    else if (sched == SCHED_DEFER) rc = stats ? wave_frame<SCHED_DEFER, true>(dev, st, a, sc, rows, (uint32_t)jobs, &n)
+                                              : wave_frame<SCHED_DEFER, false>(dev, st, a, sc, rows, (uint32_t)jobs, &n);
     else rc = stats ? wave_frame<SCHED_VOTE, true>(dev, st, a, sc, rows, (uint32_t)jobs, &n)
                     : wave_frame<SCHED_VOTE, false>(dev, st, a, sc, rows, (uint32_t)jobs, &n);
     if (rc != 0) return -1;

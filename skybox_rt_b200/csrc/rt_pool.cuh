@@ -249,7 +249,7 @@ rt_pool_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
   const uint32_t warp_in_cta = threadIdx.x >> 5;
   const size_t warp_gid = (size_t)blockIdx.x * (kPoolThreads / 32) + warp_in_cta;
   PoolCtx c = {pools + warp_in_cta, spill + warp_gid * (size_t)(kPoolSlots * kPoolSpill)};
-  Stats stats = {0u, 0u, 0u};
+  Stats stats = {0u, 0u, 0u, 0u, 0u};
   WarpPool& wp = *c.wp;
   auto collect = [&](uint32_t slot) {
     const uint32_t rec = wp.f[F_BEST_REC][slot];

@@ -101,7 +101,7 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
   Pool pool = {0u, 0u, false};
   RayState r;
   Hit best;
-  Stats stats = {0u, 0u, 0u};
+  Stats stats = {0u, 0u, 0u, 0u, 0u};
   Cursor cu;
   uint32_t my_job = 0u;   // STAGE 0: job; STAGE 1 / 2: queue index (shadow) or n_first + slot (bounce)
   uint32_t my_path = 0u;  // job id the ray belongs to (from the ray record)

@@ -40,7 +40,7 @@ constexpr int kTriAt = 8;        // SCHED_VOTE: run the triangle step once this 
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr uint32_t kChunk = 32;  // jobs per atomic fetch
 
-enum { SCHED_VOTE = 0, SCHED_WHILE = 1 };
+enum { SCHED_VOTE = 0, SCHED_WHILE = 1, SCHED_DEFER = 2 };
 
 struct WideScene {
   const float4* nodes;  // Node4 array, 8 float4 each
@@ -132,7 +132,7 @@ __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const
   const float4 ny = __ldg(np + r.oy), fy = __ldg(np + (r.oy ^ 1u));
   const float4 nz = __ldg(np + r.oz), fz = __ldg(np + (r.oz ^ 1u));
   const float4 rf = __ldg(np + 6);
-  if (STATS) stats.nodes += 1;
+  if (STATS) { stats.nodes += 1; if (step_leader()) stats.wnode += 1; }
 #define SRT_CHILD(c, tn, hit)                                                                              \
   const float tn = fmaxf(fmaxf(__fmaf_rn(nx.c, r.idir.x, -r.ood.x), __fmaf_rn(ny.c, r.idir.y, -r.ood.y)), \
                          fmaxf(__fmaf_rn(nz.c, r.idir.z, -r.ood.z), r.tmin));                             \
@@ -174,23 +174,32 @@ __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const
 }
 
 // ---- TRIANGLE step: the ray/triangle test of the triangle the lane is at ----------------------------
+// tri_test: tests triangle `ref`; true when an any-hit ray found its occluder (the ray is over).
 template <bool STATS>
-__device__ __forceinline__ void tri_step(const WideScene& sc, Cursor& cu, RayState& r, Hit& best, Stack& st,
-                                         Stats& stats) {
-  const uint32_t rec = cu.ref & 0x7FFFFFFFu;
-  if (STATS) stats.tris += 1;
+__device__ __forceinline__ bool tri_test(const WideScene& sc, uint32_t ref, RayState& r, Hit& best, Stats& stats) {
+  const uint32_t rec = ref & 0x7FFFFFFFu;
+  if (STATS) { stats.tris += 1; if (step_leader()) stats.wtri += 1; }
   if (r.any) {
     const float4* tp = sc.tris + 3 * (size_t)rec;
     const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
     float t, u, v;
     if (intersect_tri(r0, r1, r2, r.o, r.d, t, u, v) && t > r.tmin && t < best.t) {
       r.found = true;
-      st.sp = 0;
-      cu.clear();
-      return;
+      return true;
     }
   } else {
     consider(sc.tris, rec, r.o, r.d, r.tmin, best);
+  }
+  return false;
+}
+
+template <bool STATS>
+__device__ __forceinline__ void tri_step(const WideScene& sc, Cursor& cu, RayState& r, Hit& best, Stack& st,
+                                         Stats& stats) {
+  if (tri_test<STATS>(sc, cu.ref, r, best, stats)) {
+    st.sp = 0;
+    cu.clear();
+    return;
   }
   cu.go(pop_next(st, best.t));
 }
@@ -251,6 +260,42 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
         while (cu.wants_node()) node_step<STATS>(sc, cu, r, best.t, st, stats);
         while (cu.wants_tri()) tri_step<STATS>(sc, cu, r, best, st, stats);
         if (__popc(__ballot_sync(0xffffffffu, cu.busy())) < sc.tune) break;
+      }
+    }
+  } else if (SCHED == SCHED_DEFER) {
+    // Vote scheduler with one deferred triangle per lane.  A lane that reaches a triangle while the warp is busy
+    // with node steps parks it in `pend` and goes on with the next entry of its stack instead of idling; the
+    // triangle step runs once `tri_at` lanes hold a triangle (or no lane wants a node).  Closest hit is the
+    // minimum over every accepted triangle, so the order of the tests cannot change a result -- a late test only
+    // means the closest distance shrinks later and a few more nodes are visited.
+    uint32_t pend = kNone;
+    const int adv_at = sc.tune & 0xff, tri_at = (sc.tune >> 8) & 0xff;
+    for (;;) {
+      if (cu.wants_tri() && pend == kNone && st.sp > 0) {
+        pend = cu.ref;
+        cu.go(pop_next(st, best.t));
+      }
+      if (!cu.busy() && pend != kNone) { cu.go(pend); pend = kNone; }
+      const bool wn = cu.wants_node(), wt = pend != kNone || cu.wants_tri();
+      const bool wa = !cu.busy() && (have_job || !pool.dry);
+      const uint32_t mn = __ballot_sync(0xffffffffu, wn), mt = __ballot_sync(0xffffffffu, wt);
+      const uint32_t ma = __ballot_sync(0xffffffffu, wa);
+      if ((mn | mt | ma) == 0u) return;
+      if (__popc(ma) >= adv_at || (mn | mt) == 0u) {
+        advance();
+      } else if (__popc(mt) >= tri_at || mn == 0u) {
+        if (wt) {
+          const bool own = pend == kNone;
+          if (tri_test<STATS>(sc, own ? cu.ref : pend, r, best, stats)) {
+            st.sp = 0;
+            cu.clear();
+          } else if (own) {
+            cu.go(pop_next(st, best.t));
+          }
+          pend = kNone;
+        }
+      } else {
+        if (wn) node_step<STATS>(sc, cu, r, best.t, st, stats);
       }
     }
   } else {
@@ -316,7 +361,7 @@ __device__ __forceinline__ void wide_render_body(const kernel_arg_t& a, const Wi
   PathState ps = {};
   RayState r;
   Hit best;
-  Stats stats = {0u, 0u, 0u};
+  Stats stats = {0u, 0u, 0u, 0u, 0u};
   Cursor cu;
   uint32_t n_shadow = 0u, n_bounce = 0u;
   bool have_job = false;
@@ -481,7 +526,7 @@ rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
   Pool pool = {0u, 0u, false};
   RayState r;
   Hit best;
-  Stats stats = {0u, 0u, 0u};
+  Stats stats = {0u, 0u, 0u, 0u, 0u};
   Cursor cu;
   uint32_t my_ray = 0u;
   bool have_job = false;

@@ -483,6 +483,8 @@ int vx_mpm_query(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t*
     case VX_CSR_RT_NODES: *value = c[CTR_NODES]; break;
     case VX_CSR_RT_TRIS: *value = c[CTR_TRIS]; break;
     case VX_CSR_RT_NODE_BYTES: *value = dev->last_node_bytes; break;
+    case VX_CSR_RT_WARP_NODE_STEPS: *value = c[CTR_WARP_NODE_STEPS]; break;
+    case VX_CSR_RT_WARP_TRI_STEPS: *value = c[CTR_WARP_TRI_STEPS]; break;
     default: return -1;
   }
   return 0;

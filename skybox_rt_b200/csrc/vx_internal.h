@@ -40,6 +40,8 @@ enum {
   CTR_NODES = 2,
   CTR_TRIS = 3,
   CTR_CURSOR = 4,  // job cursor of the persistent kernels
+  CTR_WARP_NODE_STEPS = 5,  // warp-level node steps / triangle steps (STATS instantiations of the Node4 kernels)
+  CTR_WARP_TRI_STEPS = 6,
   CTR_PER_SM = 8,  // rays started on each SM (%smid), STATS instantiations only
   CTR_COUNT = 8 + 256
 };

@@ -87,6 +87,8 @@ def app_lib():
         L.srt_draw3d_close.argtypes = [vp]
         L.srt_draw3d_close.restype = None
         L.srt_draw3d_clear.argtypes = [vp]
+        L.srt_draw3d_set_om_override.argtypes = [vp, C.POINTER(u32)]
+        L.srt_draw3d_set_om_override.restype = None
         L.srt_draw3d_render.argtypes = [vp, C.POINTER(TraceStruct), u32, u32]
         L.srt_draw3d_prepare.argtypes = [vp, C.POINTER(TraceStruct)]
         L.srt_draw3d_submit.argtypes = [vp]
@@ -226,6 +228,11 @@ class Draw3D:
     def _ck(self, rc, what):
         if rc != 0:
             raise vx.VortexError(f"{what} failed with code {rc}")
+
+    def set_om_override(self, ov):
+        """(blend mode, blend func, blend constant, logic op) DCR values for blending draws, or None
+        (srt_draw3d_set_om_override: output-merger state a .cgltrace cannot express)."""
+        app_lib().srt_draw3d_set_om_override(self.h, (C.c_uint32 * 4)(*ov) if ov is not None else None)
 
     def clear(self):
         self._ck(app_lib().srt_draw3d_clear(self.h), "srt_draw3d_clear")

@@ -27,15 +27,17 @@ VX_CSR_MCYCLE, VX_CSR_MINSTRET = 0xB00, 0xB02
 VX_CSR_RT_RAYS_PRIMARY, VX_CSR_RT_RAYS_SHADOW, VX_CSR_RT_RAYS_BOUNCE = 0x7C0, 0x7C1, 0x7C2
 VX_CSR_RT_NODES, VX_CSR_RT_TRIS, VX_CSR_RT_ELAPSED_NS = 0x7C3, 0x7C4, 0x7C5
 VX_CSR_RT_NODE_BYTES, VX_CSR_RT_LAUNCHES = 0x7C6, 0x7C7
+VX_CSR_RT_WARP_NODE_STEPS, VX_CSR_RT_WARP_TRI_STEPS = 0x7C8, 0x7C9
 
 # back-end DCRs (csrc/vx_internal.h)
 VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE, VX_DCR_RT_PREFETCH = 0x800, 0x801, 0x802, 0x803
 VX_DCR_RT_REPACK = 0x808  # 0 = BVH2 -> Node4 on the device, 1 = on the host (A/B)
 VX_DCR_RT_SPLIT_SAMPLES = 0x807  # 0 = (pixel, sample) jobs when spp > 1, 1 = never, 2 = always
 RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL = 0, 1, 2, 3
-RT_VARIANT_WAVE, RT_VARIANT_WAVE_VOTE = 4, 5  # wavefront pipeline: trace kernels + shading passes (csrc/rt_wave.cuh)
+# wavefront pipeline: trace kernels + shading passes (csrc/rt_wave.cuh), trace kernels scheduled while-while / vote / vote + deferred triangle
+RT_VARIANT_WAVE, RT_VARIANT_WAVE_VOTE, RT_VARIANT_WAVE_DEFER = 4, 5, 6
 RT_VARIANTS = (RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL, RT_VARIANT_WAVE,
-               RT_VARIANT_WAVE_VOTE)  # every shipped kernel variant
+               RT_VARIANT_WAVE_VOTE, RT_VARIANT_WAVE_DEFER)  # every shipped kernel variant
 
 EXPORTS = [
     "vx_dev_open", "vx_dev_close", "vx_dev_caps", "vx_mem_alloc", "vx_mem_reserve", "vx_mem_free",
@@ -91,6 +93,10 @@ def lib():
                                        C.POINTER(vp), C.POINTER(vp), vp],
         }
         for name, args in sig.items():
+            if name.startswith("vx_cuda_") and not hasattr(L, name):
+                # SKYBOX_RT_LIB names the reference's own stub (oracle/_ref/libvortex.so, tests/test_gpu_ref_stub.py):
+                # it forwards the 22 reference functions to libvortex-cuda.so and knows nothing of the extensions
+                continue
             fn = getattr(L, name)
             fn.argtypes = args
             fn.restype = i
@@ -205,6 +211,11 @@ class Device:
         v = C.c_uint64()
         _check(lib().vx_mpm_query(self.handle, addr, core_id, C.byref(v)), "vx_mpm_query")
         return v.value
+
+    def node4_image_size(self):
+        """Size in bytes of the wide-node image the last ray-tracing run traversed (0 before the first one)."""
+        n = C.c_uint64()
+        return n.value if lib().vx_cuda_rt_node4_image(self.handle, None, 0, C.byref(n)) == 0 else 0
 
     def node4_image(self):
         """Bytes of the Node4 image the last ray-tracing run traversed (vx_cuda_rt_node4_image)."""

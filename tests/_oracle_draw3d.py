@@ -29,6 +29,8 @@ def _bind(path):
     L.ref_draw3d_binning.restype = C.c_int64
     L.ref_draw3d_binning.argtypes = [C.c_char_p, C.c_uint64] + [C.c_uint32] * 4 + [
         C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p, C.POINTER(C.c_uint64)]
+    L.ref_draw3d_set_om_override.argtypes = [C.POINTER(C.c_uint32)]
+    L.ref_draw3d_set_om_override.restype = None
     L.ref_draw3d_kernel_arg_size.restype = C.c_uint32
     L.ref_draw3d_prim_size.restype = C.c_uint32
     return L
@@ -55,13 +57,18 @@ def reference():
     return _libs["ref"]
 
 
-def render(L, blob, width, height, threads=4, depth=True):
-    """-> (colour [H, W] u32, depth [H, W] u32, kernel seconds); row 0 = framebuffer row 0."""
+def render(L, blob, width, height, threads=4, depth=True, om_override=None):
+    """-> (colour [H, W] u32, depth [H, W] u32, kernel seconds); row 0 = framebuffer row 0.
+    om_override = (blend mode, blend func, blend constant, logic op) DCR values for blending draws, or None."""
     fb = np.zeros((height, width), np.uint32)
     zb = np.zeros((height, width), np.uint32)
     ks = C.c_double()
-    rc = L.ref_draw3d_render(blob, len(blob), width, height, threads, 5, fb.ctypes.data,
-                             zb.ctypes.data if depth else None, C.byref(ks))
+    L.ref_draw3d_set_om_override((C.c_uint32 * 4)(*om_override) if om_override is not None else None)
+    try:
+        rc = L.ref_draw3d_render(blob, len(blob), width, height, threads, 5, fb.ctypes.data,
+                                 zb.ctypes.data if depth else None, C.byref(ks))
+    finally:
+        L.ref_draw3d_set_om_override(None)
     assert rc == 0, f"ref_draw3d_render -> {rc}"
     return fb, zb, ks.value
 
@@ -172,4 +179,30 @@ def state_variants():
     for ce, env in [(1, 3), (1, 2), (0, 3), (0, 2)]:
         v.append((f"color_enabled={ce} envmode={env}", dict(color_enabled=ce, texture_envmode=env)))
     v.append(("no texture", dict(texture_enabled=0, color_enabled=1)))
+    return v
+
+
+def om_override_variants():
+    """(label, (blend mode, blend func, blend constant, logic op)): the output-merger state the reference app never
+    programs (it is MODE_ADD only, main.cpp:271-279) but its units implement -- sim/common/graphics.cpp:366-404
+    (DoLogicOp, 16 ops), :455-472 (CONST_* factors), :477-524 (SUB / REV_SUB / MIN / MAX / LOGICOP), :611 (constant)."""
+    ADD, SUB, REV_SUB, MIN, MAX, LOGICOP = range(6)
+    ONE, SRC_A, ONE_MINUS_SRC_A, DST_RGB = 1, 6, 7, 4
+    CONST_RGB, ONE_MINUS_CONST_RGB, CONST_A, ONE_MINUS_CONST_A = 10, 11, 12, 13
+
+    def func(src_rgb, src_a, dst_rgb, dst_a):
+        return dst_a << 24 | dst_rgb << 16 | src_a << 8 | src_rgb
+    v = []
+    cst = 0x40C08020
+    for m in (SUB, REV_SUB, MIN, MAX):
+        v.append((f"mode={m}", (m << 16 | m, func(SRC_A, SRC_A, ONE_MINUS_SRC_A, ONE_MINUS_SRC_A), 0, 0)))
+        v.append((f"mode rgb={m} a=ADD one/one", (ADD << 16 | m, func(ONE, ONE, ONE, ONE), 0, 0)))
+    v.append(("mode rgb=ADD a=SUB", (SUB << 16 | ADD, func(SRC_A, ONE, DST_RGB, ONE), 0, 0)))
+    for op in range(16):
+        v.append((f"logic_op={op}", (LOGICOP << 16 | LOGICOP, func(ONE, ONE, ONE, ONE), 0, op)))
+    v.append(("logic_op rgb only", (ADD << 16 | LOGICOP, func(ONE, SRC_A, ONE, ONE_MINUS_SRC_A), 0, 6)))
+    for f in (CONST_RGB, ONE_MINUS_CONST_RGB, CONST_A, ONE_MINUS_CONST_A):
+        v.append((f"src factor={f}", (ADD << 16 | ADD, func(f, f, ONE_MINUS_SRC_A, ONE_MINUS_SRC_A), cst, 0)))
+        v.append((f"dst factor={f}", (ADD << 16 | ADD, func(SRC_A, SRC_A, f, f), cst, 0)))
+        v.append((f"factor={f} REV_SUB", (REV_SUB << 16 | REV_SUB, func(f, ONE, ONE, f), 0xFF102030, 0)))
     return v
