@@ -62,7 +62,8 @@ def parse():
                     help="draw3d: e2e leg bins on the device (vx_cuda_draw3d_binning) instead of the host pre-pass")
     ap.add_argument("--ppt", type=int, default=0, help="draw3d diagnostic: force pixels per thread (4 or 1; 0 = by grid size)")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--variant", type=int, default=0, help="0 default kernels, 1 baseline BVH2 megakernel, 2 wide while-while")
+    ap.add_argument("--variant", type=int, default=0, help="VX_DCR_RT_VARIANT: 0 default (frames: wavefront pipeline, ray lists: vote-scheduled persistent kernel), "
+                         "1 baseline BVH2 megakernel, 2 / 7 Node4 megakernel while-while / vote, 3 ray pool, 4-6 wavefront")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = N x the pixels of the same view (per-GPU work fixed), strong = the same frame split N ways")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -527,7 +528,7 @@ def native_arm(args, wl):
     return dict(rank=rank, world=world, dev_ms=dev_ms, e2e_s=e2e_s, rays_total=rays_total, kern_ms=kern_ms,
                 clocks=clocks, h2d=h2d, d2h=d2h, ctr=ctr, build_s=build_s, device_build_ms=device_build_ms, t_wall=t_wall, soup=soup, nodes=nodes,
                 tris=tris, tracer=tracer, n_nodes=len(nodes), n_tris=len(tris), stream=stream, flush=flush, launch=launch,
-                torch=torch)
+                torch=torch, arg=arg)
 
 
 def load_peaks():
@@ -599,6 +600,7 @@ def main():
                                    "sample": cpu["sample"],
                                    "single_thread": {"value": one["value"], "unit": "Mrays/s", "cores": 1, "sample": one["sample"]}}
             out["parity_check"] = parity_check(wl, tracer, cpu)
+            tracer.args.write(r["arg"])  # back to the kernel_arg_t of the timed step (the check rendered a rank strip)
         out["roofline"] = roofline_record(args, wl, r, dev, tracer, vx, cpu)
         if r["world"] == 1 and wl["mode"] != 3 and not args.no_variants:
             out["variants_ms"] = variants_ms(args, r, dev, tracer, vx)

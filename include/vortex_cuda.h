@@ -96,6 +96,35 @@ int vx_cuda_fill32(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, uint32_t
  * L2 (<= 64 MiB on B200) measures L2 -> SM bandwidth, bytes far beyond it (>= 1 GiB) HBM read bandwidth. */
 int vx_cuda_probe_read_bandwidth(vx_device_h hdevice, uint64_t bytes, uint32_t repeats, float* ms);
 
+/* ---- multi-GPU: one process (or thread) per GPU, one vx_device each, scene replicated, pixels partitioned ----
+ * No counterpart in the reference (single device).  A communicator binds this device to `num_ranks` peers over
+ * NCCL (NVLink / NVSwitch inside a box).  `id` is VX_CUDA_COMM_ID_BYTES bytes made ONCE by
+ * vx_cuda_comm_unique_id on any one rank and handed to the others by the application (a file, a pipe, an
+ * environment variable, MPI ... -- the apps use a file, apps/raytrace/main.c).  vx_cuda_comm_init is collective:
+ * every rank must call it.  libnccl.so.2 is loaded at the first of these calls; everything else in this library
+ * works without it. */
+#define VX_CUDA_COMM_ID_BYTES 128
+typedef void* vx_comm_h;
+int vx_cuda_comm_unique_id(void* id);
+int vx_cuda_comm_init(vx_device_h hdevice, const void* id, uint32_t rank, uint32_t num_ranks, vx_comm_h* hcomm);
+int vx_cuda_comm_destroy(vx_comm_h hcomm);
+
+/* Assemble a frame whose rows were rendered rank by rank (kernel_arg_t.rank_id / num_ranks / rows_per_block:
+ * row y lives on rank (y / rows_per_block) % num_ranks at local row (y / rows_per_block / num_ranks) *
+ * rows_per_block + y % rows_per_block of that rank's strip buffer).  Collective, enqueued on the launch stream
+ * behind the frame's kernels, returns at once: every rank passes its `strip` (>= srt_rank_rows() x width x 4
+ * bytes); the root also passes `frame` (>= height x width x 4 bytes, rows at pitch width x 4; NULL elsewhere),
+ * which holds the whole frame once the stream reaches this point (vx_ready_wait, or any later vx_copy_from_dev).
+ * One NCCL group of N-1 send/receive pairs plus one de-interleave kernel on the root. */
+int vx_cuda_frame_gather(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h strip, vx_buffer_h frame, uint32_t width,
+                         uint32_t height, uint32_t rows_per_block, uint32_t root);
+
+/* Concatenating gather for record lists split over the ranks (hit records of a ray list): rank r's `bytes` bytes of
+ * `src` land at offsets[r] of the root's `dst`; offsets / sizes (num_ranks entries each, sizes[r] == that rank's
+ * `bytes`) are read on the root only.  Same ordering rules as vx_cuda_frame_gather. */
+int vx_cuda_gather_bytes(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h src, uint64_t bytes, vx_buffer_h dst,
+                         const uint64_t* offsets, const uint64_t* sizes, uint32_t root);
+
 /* CUDA device ordinal the handle was opened on. */
 int vx_cuda_device(vx_device_h hdevice, int* ordinal);
 

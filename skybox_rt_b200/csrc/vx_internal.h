@@ -91,8 +91,11 @@ struct vx_device {
 // DCRs owned by this back-end (outside every range the reference decodes,
 // hw/rtl/VX_types.vh:23-29, :332-339, :353-359, :439-458).
 #define VX_DCR_RT_BASE    0x800
-#define VX_DCR_RT_VARIANT 0x800 /* 0 = default (Node4, persistent, vote scheduler), 1 = baseline BVH2 megakernel,
-                                   2 = Node4 persistent while-while (A/B)                                    */
+#define VX_DCR_RT_VARIANT 0x800 /* 0 = default: the measured best per kind of work (frames: 4, ray lists: 7);
+                                   1 = baseline BVH2 megakernel, 2 = Node4 persistent megakernel while-while,
+                                   3 = ray pool (ray lists), 4 / 5 / 6 = wavefront pipeline with while-while /
+                                   vote / vote + deferred-triangle trace kernels, 7 = Node4 persistent megakernel,
+                                   vote scheduler (the round-1 default)                                       */
 #define VX_DCR_RT_STATS   0x801 /* 1 = count node fetches / triangle tests (slower)               */
 #define VX_DCR_RT_KEEP_ACTIVE 0x802 /* tuning: refill threshold of the persistent kernels (1..32), 0 = default */
 #define VX_DCR_RT_PREFETCH 0x803 /* 1 = warm L2 with the scene before tracing when it fits (measured: no gain, off by default) */

@@ -36,8 +36,9 @@ VX_DCR_RT_SPLIT_SAMPLES = 0x807  # 0 = (pixel, sample) jobs when spp > 1, 1 = ne
 RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL = 0, 1, 2, 3
 # wavefront pipeline: trace kernels + shading passes (csrc/rt_wave.cuh), trace kernels scheduled while-while / vote / vote + deferred triangle
 RT_VARIANT_WAVE, RT_VARIANT_WAVE_VOTE, RT_VARIANT_WAVE_DEFER = 4, 5, 6
+RT_VARIANT_MEGA_VOTE = 7  # persistent megakernel, vote scheduler (the round-1 default); 0 now picks 4 for frames, 7 for ray lists
 RT_VARIANTS = (RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL, RT_VARIANT_WAVE,
-               RT_VARIANT_WAVE_VOTE, RT_VARIANT_WAVE_DEFER)  # every shipped kernel variant
+               RT_VARIANT_WAVE_VOTE, RT_VARIANT_WAVE_DEFER, RT_VARIANT_MEGA_VOTE)  # every shipped kernel variant
 
 EXPORTS = [
     "vx_dev_open", "vx_dev_close", "vx_dev_caps", "vx_mem_alloc", "vx_mem_reserve", "vx_mem_free",
