@@ -67,6 +67,8 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = N x the pixels of the same view (per-GPU work fixed), strong = the same frame split N ways")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true",
+                    help="skip the strong-scaling legs (C4 frame and C5 ray list split over the N GPUs) of the default run")
     ap.add_argument("--no-variants", action="store_true", help="skip the untimed A/B steps of the other kernel variants")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
     ap.add_argument("--keep-active", type=int, default=0, help="diagnostic: refill threshold DCR (0 = default)")
@@ -360,7 +362,9 @@ class DevMem:
                                          "version": 2, "strides": None}
 
 
-def native_arm(args, wl):
+def native_arm(args, wl, steps, solo=False, sample_clocks=True):
+    """One workload measured on this process' GPU (all ranks call it; `solo`: rank 0 alone runs the whole workload,
+    the others return None -- the 1-GPU leg of a strong-scaling pair measured inside an N-GPU run)."""
     import torch
     import torch.distributed as dist
 
@@ -371,11 +375,10 @@ def native_arm(args, wl):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    os.environ["VX_CUDA_DEVICE"] = str(local)
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torch.distributed.run)"
+    if solo:
+        if rank != 0:
+            return None
+        world = 1
 
     soup, nodes, tris, build_s = build_scene(wl, rt)
     device_build_ms = None
@@ -395,9 +398,10 @@ def native_arm(args, wl):
     dev.dcr_write(vx.VX_DCR_RT_SPLIT_SAMPLES, args.split_samples)
     stream = torch.cuda.ExternalStream(dev.cuda_stream(), device=torch.device("cuda", local))
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.int32, device="cuda")
-    launches = 0
+    extra = []  # buffers / communicators to release with the tracer
 
     rays_mode = wl["mode"] == 3
+    gather = None
     if rays_mode:
         n_total = wl["rays"]
         n_local = n_total // world
@@ -408,6 +412,7 @@ def native_arm(args, wl):
         host_hits = torch.empty(n_local * HIT.itemsize, dtype=torch.uint8).pin_memory()
         ray_buf = dev.alloc(n_local * RAY.itemsize, vx.VX_MEM_READ)
         hit_buf = dev.alloc(n_local * HIT.itemsize)
+        extra += [ray_buf, hit_buf]
         ray_buf.write(host_rays)
         from skybox_rt_b200.formats import KernelArg
         arg = KernelArg()
@@ -418,53 +423,88 @@ def native_arm(args, wl):
         args_buf = dev.upload(arg)
         tracer.args = args_buf
         h2d, d2h = n_local * RAY.itemsize + 192, n_local * HIT.itemsize
+        pipeline_depth = 1
 
         def launch():
             dev.start(tracer.kernel, args_buf)
 
-        def e2e_step(i):
+        def e2e_serial(i):
             ray_buf.write(host_rays)
             args_buf.write(arg)
             dev.start(tracer.kernel, args_buf)
             dev.ready_wait()
             hit_buf.read(host_hits)
-        gather = None
+
+        def e2e_loop(k):  # a ray list has no next frame to overlap with: the loop is the serial one
+            for i in range(k):
+                e2e_serial(i)
     else:
         W, H = wl["w"], wl["h"]
         arg = rt.make_arg(W, H, wl["mode"], spp=wl["spp"], seed=1234, scene=wl["scene"], rank=rank,
                           num_ranks=world, rows_per_block=ROWS_PER_BLOCK)
         rows = tracer.start(arg)  # binds cbuf + args, first (cold) frame
         dev.ready_wait()
-        strip = torch.as_tensor(DevMem(tracer.cbuf.address, rows * W * 4), device="cuda")
-        max_rows = max(rank_rows(H, ROWS_PER_BLOCK, world, r) for r in range(world))
-        host_frame = torch.empty(H * W, dtype=torch.int32).pin_memory()
+        host_frames = [torch.empty(H * W, dtype=torch.int32).pin_memory() for _ in range(2)]
         h2d, d2h = 192, (H * W * 4 if rank == 0 else 0)
+        pipeline_depth = 2
         if world > 1:
-            # one NCCL gather of the strips per frame, on the render stream
-            from skybox_rt_b200.multi import FrameGather
-            fg = FrameGather(W, H, ROWS_PER_BLOCK, torch.device("cuda", local))
+            # one NCCL exchange of the strips per frame, queued on the render stream by the C entry
+            # vx_cuda_frame_gather; torch.distributed only carried the communicator id
+            from skybox_rt_b200.multi import NcclFrameGather
+            fg = NcclFrameGather(dev, W, H, ROWS_PER_BLOCK)
+            frames = [fg.frame, dev.alloc(H * W * 4) if rank == 0 else None]
+            extra += [fg] + ([frames[1]] if rank == 0 else [])
 
-            def gather():
-                return fg.gather(strip.view(torch.int32))
+            def gather(slot=0):
+                fg.comm.frame_gather(tracer.cbuf, frames[slot], W, H, ROWS_PER_BLOCK, 0)
+            targets = None
         else:
-            gather = None
+            targets = [tracer.cbuf, dev.alloc(max(rows, 1) * W * 4)]  # double-buffered render target
+            extra.append(targets[1])
 
         def launch():
             dev.start(tracer.kernel, tracer.args)
 
-        def e2e_step(i):
+        def e2e_serial(i):
             arg.seed = 1234 + i  # a new kernel_arg_t every frame, from the host
             tracer.args.write(arg)
             dev.start(tracer.kernel, tracer.args)
             if gather:
-                with torch.cuda.stream(stream):
-                    frame_dev = gather()  # strips -> rank 0, de-interleaved on the device
-                    if rank == 0:         # one D2H copy of the assembled frame
-                        host_frame.copy_(frame_dev.view(-1), non_blocking=True)
-                stream.synchronize()
+                gather(0)
+                dev.ready_wait()
+                if rank == 0:  # one D2H copy of the assembled frame
+                    frames[0].read(host_frames[0])
             else:
                 dev.ready_wait()
-                tracer.cbuf.read(host_frame)
+                tracer.cbuf.read(host_frames[0])
+
+        def e2e_loop(k):
+            """The render loop an application runs: frame i+1 is queued while frame i travels to the host
+            (vx_cuda_copy_from_dev_async, two render targets / two host frames).  Every frame's kernel_arg_t upload
+            and read-back are inside the timed region; the loop ends when the last frame is on the host."""
+            tickets = [None, None]
+            for i in range(k):
+                slot = i & 1
+                if tickets[slot] is not None:
+                    dev.copy_wait(tickets[slot])  # the app is done with frame i-2; its buffers are free again
+                arg.seed = 1234 + i
+                if targets:
+                    arg.cbuf_addr = targets[slot].address
+                tracer.args.write(arg)
+                dev.start(tracer.kernel, tracer.args)
+                if gather:
+                    gather(slot)
+                    if rank == 0:
+                        tickets[slot] = frames[slot].read_async(host_frames[slot])
+                else:
+                    tickets[slot] = targets[slot].read_async(host_frames[slot])
+            for t in tickets:
+                if t is not None:
+                    dev.copy_wait(t)
+            dev.ready_wait()
+            if targets:
+                arg.cbuf_addr = targets[0].address
+                tracer.args.write(arg)
 
     def barrier():
         if world > 1:
@@ -476,18 +516,18 @@ def native_arm(args, wl):
         return c["rays_primary"] + c["rays_shadow"] + c["rays_bounce"], c
 
     # ---- warm-up --------------------------------------------------------------------------
-    with torch.cuda.stream(stream):
-        for _ in range(max(args.warmup, 3)):
-            launch()
-            if gather:
-                gather()
+    for _ in range(max(args.warmup, 3)):
+        launch()
+        if gather:
+            gather()
     barrier()
     rays_per_step, ctr = step_rays()
 
     # ---- timed: K steps, device time on the launch stream, L2 flushed before each ------------
-    sampler = ClockSampler(local)
-    sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    sampler = ClockSampler(local) if sample_clocks else None
+    if sampler:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     barrier()
     t_wall = time.perf_counter()
     with torch.cuda.stream(stream):
@@ -501,34 +541,89 @@ def native_arm(args, wl):
             b.record(stream)
     barrier()
     t_wall = time.perf_counter() - t_wall
-    clocks = sampler.stop()
+    clocks = sampler.stop() if sampler else None
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
     kern_ns = dev.mpm_query(vx.VX_CSR_RT_ELAPSED_NS)  # vx_start..end of the last step, without gather
 
     # ---- e2e: host buffers, copies inside the timed region, wall clock ---------------------------
-    for i in range(2):
-        e2e_step(i)
+    e2e_loop(2)
     barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        e2e_step(i)
+    e2e_loop(steps)
     barrier()
     e2e_s = time.perf_counter() - t0
+    for i in range(2):
+        e2e_serial(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        e2e_serial(i)
+    barrier()
+    e2e_serial_s = time.perf_counter() - t0
 
-    t = torch.tensor([dev_ms, e2e_s, float(rays_per_step), kern_ns * 1e-6], dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, e2e_s, float(rays_per_step), kern_ns * 1e-6, e2e_serial_s], dtype=torch.float64, device="cuda")
     if world > 1:
         mx = t.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = t.clone()
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        dev_ms, e2e_s, kern_ms = mx[0].item(), mx[1].item(), mx[3].item()
+        dev_ms, e2e_s, kern_ms, e2e_serial_s = mx[0].item(), mx[1].item(), mx[3].item(), mx[4].item()
         rays_total = sm[2].item()
     else:
         rays_total, kern_ms = float(rays_per_step), kern_ns * 1e-6
-    return dict(rank=rank, world=world, dev_ms=dev_ms, e2e_s=e2e_s, rays_total=rays_total, kern_ms=kern_ms,
-                clocks=clocks, h2d=h2d, d2h=d2h, ctr=ctr, build_s=build_s, device_build_ms=device_build_ms, t_wall=t_wall, soup=soup, nodes=nodes,
+    return dict(rank=rank, world=world, dev_ms=dev_ms, e2e_s=e2e_s, e2e_serial_s=e2e_serial_s, rays_total=rays_total,
+                kern_ms=kern_ms, clocks=clocks, h2d=h2d, d2h=d2h, ctr=ctr, build_s=build_s, steps=steps,
+                device_build_ms=device_build_ms, t_wall=t_wall, soup=soup, nodes=nodes, pipeline_depth=pipeline_depth,
                 tris=tris, tracer=tracer, n_nodes=len(nodes), n_tris=len(tris), stream=stream, flush=flush, launch=launch,
-                torch=torch, arg=arg)
+                torch=torch, arg=arg, extra=extra)
+
+
+def release(r):
+    if r is None:
+        return
+    for x in r["extra"]:
+        if hasattr(x, "close"):
+            x.close()
+        else:
+            x.free()
+    r["tracer"].close()
+
+
+def strong_legs(args):
+    """north_star: "image tiles partitioned across the GPUs of one box ... scaling >= 7x on 8 GPUs" is STRONG scaling
+    of one fixed job.  For C4 (the 4K x 8 spp frame) and C5 (the 64 Mi-ray list), in this same run: the job split over
+    all N ranks (device time incl. the frame gather, max over ranks) and the whole job on rank 0 alone, with a clock
+    record each.  At N = 1 the pair collapses to the single-GPU figure."""
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    out = {}
+    for key in ("c4", "c5"):
+        wl = dict(WORKLOADS[key])
+        r = native_arm(args, wl, steps=5)
+        K = r["steps"]
+        leg = None
+        if r["rank"] == 0:
+            ms = r["dev_ms"] / K
+            leg = {"workload": wl["name"], "n_gpus": world, "steps": K, "ms_per_step": ms,
+                   "value": r["rays_total"] / (ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                   "e2e_ms_per_step": r["e2e_s"] / K * 1e3, "e2e_value": r["rays_total"] / (r["e2e_s"] / K) / 1e6,
+                   "e2e_serial_ms_per_step": r["e2e_serial_s"] / K * 1e3,
+                   "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"], "clocks": r["clocks"]}
+        release(r)
+        if world > 1:
+            dist.barrier()
+            r1 = native_arm(args, wl, steps=3, solo=True)
+            if r1 is not None:
+                ms1 = r1["dev_ms"] / r1["steps"]
+                leg.update(n1_ms_per_step=ms1, n1_value=r1["rays_total"] / (ms1 * 1e-3) / 1e6, n1_clocks=r1["clocks"],
+                           n1_e2e_ms_per_step=r1["e2e_s"] / r1["steps"] * 1e3,
+                           speedup_vs_n1=ms1 / leg["ms_per_step"],
+                           e2e_speedup_vs_n1=(r1["e2e_s"] / r1["steps"] * 1e3) / leg["e2e_ms_per_step"])
+                release(r1)
+            dist.barrier()
+        if leg is not None:
+            out[key] = leg
+    return out
 
 
 def load_peaks():
@@ -566,7 +661,16 @@ def main():
         reference_arm(args, wl)
         return
     from skybox_rt_b200 import vortex as vx
-    r = native_arm(args, wl)
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ["VX_CUDA_DEVICE"] = str(local)
+    torch.cuda.set_device(local)
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torch.distributed.run)"
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    r = native_arm(args, wl, steps=args.steps)
     tracer, dev = r["tracer"], r["tracer"].dev
     out = None
     if r["rank"] == 0:
@@ -586,7 +690,12 @@ def main():
                                     "BVH replicated, one NCCL gather per frame" if r["world"] > 1 else "single GPU"},
             "rays": {k: r["ctr"][k] for k in ("rays_primary", "rays_shadow", "rays_bounce")},
             "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "ms_per_step": r["e2e_s"] / K * 1e3},
+                    "ms_per_step": r["e2e_s"] / K * 1e3, "frames_in_flight": r["pipeline_depth"],
+                    "loop": "kernel_arg_t upload -> vx_start -> (frame gather) -> vx_cuda_copy_from_dev_async into pinned "
+                            "host memory, frame i+1 queued while frame i travels; ends when the last frame is on the host"
+                            if r["pipeline_depth"] > 1 else "rays upload -> vx_start -> vx_ready_wait -> hits read-back",
+                    "serial_ms_per_step": r["e2e_serial_s"] / K * 1e3,
+                    "serial_value": r["rays_total"] / (r["e2e_serial_s"] / K) / 1e6},
             "gpu_launches": int(dev.mpm_query(vx.VX_CSR_RT_LAUNCHES)) * K,
             "clocks": r["clocks"],
             "host_prepass_s": {"bvh2_build": r["build_s"]},
@@ -604,7 +713,11 @@ def main():
         out["roofline"] = roofline_record(args, wl, r, dev, tracer, vx, cpu)
         if r["world"] == 1 and wl["mode"] != 3 and not args.no_variants:
             out["variants_ms"] = variants_ms(args, r, dev, tracer, vx)
-    tracer.close()
+    release(r)
+    if not args.no_strong and args.workload == "c3" and args.scaling == "weak":
+        legs = strong_legs(args)
+        if out is not None:
+            out["strong"] = legs
     if r["world"] > 1:
         import torch.distributed as dist
         dist.barrier()

@@ -24,6 +24,16 @@ int vx_cuda_stream(vx_device_h hdevice, void** stream);
 int vx_cuda_host_register(vx_device_h hdevice, void* ptr, uint64_t size);
 int vx_cuda_host_unregister(vx_device_h hdevice, void* ptr);
 
+/* Asynchronous read-back for render loops.  vx_copy_from_dev blocks until the bytes are on the host, so a loop of
+ * vx_start / vx_copy_from_dev leaves the device idle during every transfer.  This variant orders the copy after
+ * everything queued on the launch stream so far, runs it on a second stream and returns at once with a ticket:
+ * frames started afterwards overlap the transfer.  host_ptr should be page-locked (vx_cuda_host_register) -- a
+ * pageable destination makes the copy synchronous.  The app must not let later work overwrite the source range, nor
+ * read host_ptr, before vx_cuda_copy_wait(ticket) returns (double-buffer the render target).  Up to 16 copies
+ * may be in flight; vx_dev_close waits for all of them. */
+int vx_cuda_copy_from_dev_async(void* host_ptr, vx_buffer_h hbuffer, uint64_t src_offset, uint64_t size, uint64_t* ticket);
+int vx_cuda_copy_wait(vx_device_h hdevice, uint64_t ticket);
+
 /* Totals of the performance monitor (VX_DCR_BASE_MPM_CLASS != 0, include/skybox_rt.h) accumulated over every
  * profiled run since vx_dev_open: out[i] = slot i below for i < count.  vx_dump_perf prints from these. */
 enum {

@@ -92,7 +92,7 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
   Stack st;
   st.base = (uint32_t)__cvta_generic_to_shared(s_stack + threadIdx.x);
   st.spill = spill;
-  st.sp = 0;
+  st.reset();
   const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
   const uint32_t seed_hash = mix32(a.seed);
   const Camera cam = make_camera(a);
@@ -131,7 +131,7 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
           if (STATS) stats.rays += 1;
           ray_setup(r, cam.eye, wave_camera_dir(a, cam, seed_hash, x, global_row(a, ly), s), 0.0f, false);
           best.t = kTMax; best.prim = SRT_MISS; best.rec = SRT_MISS;
-          st.sp = 0;
+          st.reset();
           cu.go(0u);
         }
       } else {
@@ -143,7 +143,7 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
         if (STATS) stats.rays += 1;
         ray_setup(r, mk(r0.x, r0.y, r0.z), mk(r1.x, r1.y, r1.z), 0.0f, shadow);
         best.t = r1.w; best.prim = SRT_MISS; best.rec = SRT_MISS;
-        st.sp = 0;
+        st.reset();
         cu.go(0u);
       }
     }
@@ -190,7 +190,30 @@ rt_wave_shade1_kernel(const __grid_constant__ kernel_arg_t a, const float4* __re
   }
   const uint32_t ss = queue_slot(&wb.ctl->n_shadow1, want_shadow);
   if (want_shadow) { wb.q_shadow[2 * (size_t)ss] = s0; wb.q_shadow[2 * (size_t)ss + 1] = s1; }
+#ifdef SRT_NO_BOUNCE_SORT
   const uint32_t bs = queue_slot(&wb.ctl->n_bounce, want_bounce);
+#else
+  // Bounce rays leave neighbouring pixels in unrelated directions.  The CTA's (up to 256) rays -- eight adjacent
+  // 8x4 tiles, so their origins are close -- are appended to the queue grouped by direction octant: the 32
+  // consecutive rays a trace warp fetches then share the near/far child order of every node and stay together
+  // for more of the tree.  A counting sort in shared memory, one global atomic per CTA; which slot a ray gets
+  // cannot change its result (results are stored by slot / job).
+  __shared__ uint32_t s_cnt[8], s_off[8];
+  if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  const uint32_t key = (b1.x < 0.0f ? 1u : 0u) | (b1.y < 0.0f ? 2u : 0u) | (b1.z < 0.0f ? 4u : 0u);
+  uint32_t pos = 0;
+  if (want_bounce) pos = atomicAdd(&s_cnt[key], 1u);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t total = 0;
+    for (int k = 0; k < 8; ++k) { s_off[k] = total; total += s_cnt[k]; }
+    const uint32_t base = total ? atomicAdd(&wb.ctl->n_bounce, total) : 0u;
+    for (int k = 0; k < 8; ++k) s_off[k] += base;
+  }
+  __syncthreads();
+  const uint32_t bs = s_off[key] + pos;
+#endif
   if (want_bounce) { wb.q_bounce[2 * (size_t)bs] = b0; wb.q_bounce[2 * (size_t)bs + 1] = b1; }
 }
 

@@ -94,29 +94,39 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
 }
 
 // One traversal stack per thread: shared entries first ([entry][thread]), local spill above.  The spill
-// array is a separate kernel-local array (passed by pointer) so that `sp` and `base` stay in registers.
+// array is a separate kernel-local array (passed by pointer) so that `top` and `base` stay in registers.
+// The stack pointer IS the shared-space byte address of the next free entry (entries of one thread lie
+// kStackStride apart): a push is a store and one add, and the depth never has to be turned into an address.
+// Addresses at or above base + kSmStack * kStackStride do not exist in shared memory; they stand for the
+// entries of the spill array.
 constexpr uint32_t kStackStride = kWideThreads * 8u;  // bytes between consecutive entries of one thread
+constexpr uint32_t kSmStackBytes = (uint32_t)kSmStack * kStackStride;
 struct Stack {
   uint32_t base;  // shared-space byte address of this thread's entry 0
+  uint32_t top;   // address of the next free entry
   uint2* spill;   // kLocalStack entries in local memory
-  int sp;
+  __device__ __forceinline__ void reset() { top = base; }
+  __device__ __forceinline__ bool empty() const { return top == base; }
   __device__ __forceinline__ void push_slow(uint32_t ref, float tn) {
-    if (sp < kSmStack) sts64(base + (uint32_t)sp * kStackStride, ref, __float_as_uint(tn));
-    else if (sp < kSmStack + kLocalStack) spill[sp - kSmStack] = make_uint2(ref, __float_as_uint(tn));
+    const uint32_t off = top - base;
+    if (off < kSmStackBytes) sts64(top, ref, __float_as_uint(tn));
+    else if (off < kSmStackBytes + (uint32_t)kLocalStack * kStackStride) spill[(off - kSmStackBytes) / kStackStride] = make_uint2(ref, __float_as_uint(tn));
     else __trap();  // the host checked 3 * depth <= capacity before launching
-    ++sp;
+    top += kStackStride;
   }
   __device__ __forceinline__ uint2 pop() {
-    --sp;
-    return sp < kSmStack ? lds64(base + (uint32_t)sp * kStackStride) : spill[sp - kSmStack];
+    top -= kStackStride;
+    const uint32_t off = top - base;
+    return off < kSmStackBytes ? lds64(top) : spill[(off - kSmStackBytes) / kStackStride];
   }
 };
 
 // Pop until an entry survives the current closest distance; kNone when the stack is empty.
 __device__ __forceinline__ uint32_t pop_next(Stack& st, float best_t) {
-  while (st.sp > 0) {
+  const float limit = best_t * kPad;
+  while (!st.empty()) {
     const uint2 e = st.pop();
-    if (__uint_as_float(e.y) <= best_t * kPad) return e.x;
+    if (__uint_as_float(e.y) <= limit) return e.x;
   }
   return kNone;
 }
@@ -127,11 +137,13 @@ __device__ __forceinline__ uint32_t pop_next(Stack& st, float best_t) {
 template <bool STATS>
 __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const RayState& r, float best_t, Stack& st,
                                           Stats& stats) {
-  const float4* np = sc.nodes + (size_t)cu.ref * 8;
-  const float4 nx = __ldg(np + r.ox), fx = __ldg(np + (r.ox ^ 1u));
-  const float4 ny = __ldg(np + r.oy), fy = __ldg(np + (r.oy ^ 1u));
-  const float4 nz = __ldg(np + r.oz), fz = __ldg(np + (r.oz ^ 1u));
-  const float4 rf = __ldg(np + 6);
+  // float4 index of the node's first plane, kept in 32 bits (the host refuses images of 2^32 float4 = 64 GiB):
+  // every load address is one 32-bit add / xor and one widening multiply-add onto the uniform base pointer
+  const uint32_t n0 = cu.ref * 8u;
+  const float4 nx = __ldg(sc.nodes + (n0 + r.ox)), fx = __ldg(sc.nodes + ((n0 + r.ox) ^ 1u));
+  const float4 ny = __ldg(sc.nodes + (n0 + r.oy)), fy = __ldg(sc.nodes + ((n0 + r.oy) ^ 1u));
+  const float4 nz = __ldg(sc.nodes + (n0 + r.oz)), fz = __ldg(sc.nodes + ((n0 + r.oz) ^ 1u));
+  const float4 rf = __ldg(sc.nodes + (n0 + 6u));
   if (STATS) { stats.nodes += 1; if (step_leader()) stats.wnode += 1; }
 #define SRT_CHILD(c, tn, hit)                                                                              \
   const float tn = fmaxf(fmaxf(__fmaf_rn(nx.c, r.idir.x, -r.ood.x), __fmaf_rn(ny.c, r.idir.y, -r.ood.y)), \
@@ -148,22 +160,25 @@ __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const
     return;
   }
   // nearest hit child becomes the next position; the other hit children are pushed with their
-  // entry distance (checked again against the then-current closest distance when popped)
+  // entry distance (checked again against the then-current closest distance when popped).
+  // Written as compare + select chains (no data-dependent branch: the four-way pick used to compile
+  // into a branch tree that the lanes of a warp took in different directions).
   const float inf = __int_as_float(0x7f800000);
   const float k0 = h0 ? t0 : inf, k1 = h1 ? t1 : inf, k2 = h2 ? t2 : inf, k3 = h3 ? t3 : inf;
   const float kmin = fminf(fminf(k0, k1), fminf(k2, k3));
-  const int sel = k0 == kmin ? 0 : (k1 == kmin ? 1 : (k2 == kmin ? 2 : 3));
   const uint32_t c0 = __float_as_uint(rf.x), c1 = __float_as_uint(rf.y), c2 = __float_as_uint(rf.z),
                  c3 = __float_as_uint(rf.w);
-  const uint32_t next = sel == 0 ? c0 : (sel == 1 ? c1 : (sel == 2 ? c2 : c3));
-  const bool p0 = h0 && sel != 0, p1 = h1 && sel != 1, p2 = h2 && sel != 2, p3 = h3 && sel != 3;
-  if (st.sp + 3 <= kSmStack) {  // common case: predicated stores, no branches
-    uint32_t top = st.base + (uint32_t)st.sp * kStackStride;
-    if (p3) { sts64(top, c3, __float_as_uint(t3)); top += kStackStride; }
-    if (p2) { sts64(top, c2, __float_as_uint(t2)); top += kStackStride; }
-    if (p1) { sts64(top, c1, __float_as_uint(t1)); top += kStackStride; }
-    if (p0) { sts64(top, c0, __float_as_uint(t0)); }
-    st.sp += (int)p0 + (int)p1 + (int)p2 + (int)p3;
+  const bool e0 = k0 == kmin, e1 = !e0 && k1 == kmin, e2 = !e0 && !e1 && k2 == kmin;  // lowest index wins a tie
+  uint32_t next = c3;
+  next = e2 ? c2 : next;
+  next = e1 ? c1 : next;
+  next = e0 ? c0 : next;
+  const bool p0 = h0 && !e0, p1 = h1 && !e1, p2 = h2 && !e2, p3 = h3 && (e0 || e1 || e2);
+  if (st.top - st.base <= kSmStackBytes - 3u * kStackStride) {  // common case: predicated stores, no branches
+    if (p3) { sts64(st.top, c3, __float_as_uint(t3)); st.top += kStackStride; }
+    if (p2) { sts64(st.top, c2, __float_as_uint(t2)); st.top += kStackStride; }
+    if (p1) { sts64(st.top, c1, __float_as_uint(t1)); st.top += kStackStride; }
+    if (p0) { sts64(st.top, c0, __float_as_uint(t0)); st.top += kStackStride; }
   } else {
     if (p3) st.push_slow(c3, t3);
     if (p2) st.push_slow(c2, t2);
@@ -197,7 +212,7 @@ template <bool STATS>
 __device__ __forceinline__ void tri_step(const WideScene& sc, Cursor& cu, RayState& r, Hit& best, Stack& st,
                                          Stats& stats) {
   if (tri_test<STATS>(sc, cu.ref, r, best, stats)) {
-    st.sp = 0;
+    st.reset();
     cu.clear();
     return;
   }
@@ -253,6 +268,35 @@ template <int SCHED, bool STATS, class Advance>
 __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RayState& r, Hit& best, Stack& st,
                                          Stats& stats, const Pool& pool, const bool& have_job, Advance advance) {
   if (SCHED == SCHED_WHILE) {
+#ifdef SRT_SPEC
+    // while-while with one postponed triangle per lane (speculative traversal): a lane that reaches a triangle
+    // while others of its warp still walk nodes parks it and walks on; it leaves the node loop when it meets a
+    // second triangle or runs out of nodes.  The triangle phase then tests the parked triangle of (nearly) every
+    // lane in one step.  Test order cannot change a result (closest hit = minimum over all accepted triangles).
+    uint32_t pend = kNone;
+    for (;;) {
+      advance();
+      if (pool.dry && !__any_sync(0xffffffffu, have_job)) return;
+      for (;;) {
+        while (cu.wants_node()) {
+          node_step<STATS>(sc, cu, r, best.t, st, stats);
+          if (pend == kNone && cu.wants_tri()) {
+            pend = cu.ref;
+            cu.go(pop_next(st, best.t));
+          }
+        }
+        if (pend != kNone) {
+          if (tri_test<STATS>(sc, pend, r, best, stats)) {
+            st.reset();
+            cu.clear();
+          }
+          pend = kNone;
+        }
+        while (cu.wants_tri()) tri_step<STATS>(sc, cu, r, best, st, stats);
+        if (__popc(__ballot_sync(0xffffffffu, cu.busy())) < sc.tune) break;
+      }
+    }
+#else
     for (;;) {
       advance();
       if (pool.dry && !__any_sync(0xffffffffu, have_job)) return;
@@ -262,6 +306,7 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
         if (__popc(__ballot_sync(0xffffffffu, cu.busy())) < sc.tune) break;
       }
     }
+#endif
   } else if (SCHED == SCHED_DEFER) {
     // Vote scheduler with one deferred triangle per lane.  A lane that reaches a triangle while the warp is busy
     // with node steps parks it in `pend` and goes on with the next entry of its stack instead of idling; the
@@ -271,7 +316,7 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
     uint32_t pend = kNone;
     const int adv_at = sc.tune & 0xff, tri_at = (sc.tune >> 8) & 0xff;
     for (;;) {
-      if (cu.wants_tri() && pend == kNone && st.sp > 0) {
+      if (cu.wants_tri() && pend == kNone && !st.empty()) {
         pend = cu.ref;
         cu.go(pop_next(st, best.t));
       }
@@ -287,7 +332,7 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
         if (wt) {
           const bool own = pend == kNone;
           if (tri_test<STATS>(sc, own ? cu.ref : pend, r, best, stats)) {
-            st.sp = 0;
+            st.reset();
             cu.clear();
           } else if (own) {
             cu.go(pop_next(st, best.t));
@@ -353,7 +398,7 @@ __device__ __forceinline__ void wide_render_body(const kernel_arg_t& a, const Wi
   Stack st;
   st.base = (uint32_t)__cvta_generic_to_shared(s_stack + threadIdx.x);
   st.spill = spill;
-  st.sp = 0;
+  st.reset();
   const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
   const uint32_t seed_hash = mix32(a.seed);
   const Camera cam = make_camera(a);
@@ -373,7 +418,7 @@ __device__ __forceinline__ void wide_render_body(const kernel_arg_t& a, const Wi
     if (STATS) stats.rays += 1;
     ray_setup(r, o, d, 0.0f, any);
     best.t = tmax; best.prim = SRT_MISS; best.rec = 0u;
-    st.sp = 0;
+    st.reset();
     cu.go(0u);  // root
   };
   auto start_primary = [&]() {
@@ -522,7 +567,7 @@ rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
   Stack st;
   st.base = (uint32_t)__cvta_generic_to_shared(s_stack + threadIdx.x);
   st.spill = spill;
-  st.sp = 0;
+  st.reset();
   Pool pool = {0u, 0u, false};
   RayState r;
   Hit best;
@@ -547,7 +592,7 @@ rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
       if (STATS) stats.rays += 1;
       ray_setup(r, mk(r0.x, r0.y, r0.z), mk(r1.x, r1.y, r1.z), r0.w, false);
       best.t = r1.w; best.u = 0.0f; best.v = 0.0f; best.prim = SRT_MISS; best.rec = 0u;
-      st.sp = 0;
+      st.reset();
       cu.go(0u);
     }
   };

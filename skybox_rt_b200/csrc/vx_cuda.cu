@@ -104,6 +104,8 @@ int vx_dev_open(vx_device_h* hdevice) {
   dev->bytes_used = 0;
   dev->rt = nullptr;
   dev->raster = nullptr;
+  dev->copy_stream = nullptr;
+  dev->copy_next_ticket = 0;
   dev->last_raster_tiles = 0;
   dev->last_raster_fragments = dev->last_raster_tests = 0;
   dev->run_recorded = false;
@@ -143,6 +145,13 @@ int vx_dev_close(vx_device_h hdevice) {
   vx_device* dev = as_dev(hdevice);
   cudaSetDevice(dev->cuda_dev);
   cudaStreamSynchronize(dev->stream);
+  if (dev->copy_stream) {
+    cudaStreamSynchronize(dev->copy_stream);
+    cudaEventDestroy(dev->copy_fork);
+    for (cudaEvent_t e : dev->copy_done) cudaEventDestroy(e);
+    cudaStreamDestroy(dev->copy_stream);
+    dev->copy_stream = nullptr;
+  }
   if (env_int("VORTEX_PROFILING", 0) != 0) vx_dump_perf(hdevice, stdout);  // stub/vortex.cpp:99-104
   srt::rt_destroy(dev);
   srt::raster_destroy(dev);
@@ -237,9 +246,17 @@ int vx_copy_to_dev(vx_buffer_h hbuffer, const void* host_ptr, uint64_t dst_offse
   if (dst_offset + size > b->size) return -1;  // callbacks.inc:155-156
   vx_device* dev = b->dev;
   VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
-  VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, host_ptr, size, cudaMemcpyHostToDevice, dev->stream));
-  VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
-  if (b->shadow) memcpy(b->shadow + dst_offset, host_ptr, size);
+  if (b->shadow) {
+    // small host-written buffers (kernel arguments, kernel images): the bytes go to the shadow first and travel from
+    // there.  The shadow is pageable memory, which cudaMemcpyAsync stages before it returns, so the caller's buffer
+    // and the shadow are both free on return WITHOUT waiting for the frames still queued on the stream -- a render
+    // loop that uploads a new kernel_arg_t per frame keeps the device busy.
+    memcpy(b->shadow + dst_offset, host_ptr, size);
+    VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, b->shadow + dst_offset, size, cudaMemcpyHostToDevice, dev->stream));
+  } else {
+    VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, host_ptr, size, cudaMemcpyHostToDevice, dev->stream));
+    VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
+  }
   b->generation++;
   return 0;
 }
@@ -601,6 +618,40 @@ int vx_cuda_host_unregister(vx_device_h hdevice, void* ptr) {
     cudaGetLastError();
     return -1;
   }
+  return 0;
+}
+
+// Asynchronous read-back: ordered after everything queued on the launch stream so far, executed on a second stream so
+// that the frames queued afterwards overlap the transfer.
+int vx_cuda_copy_from_dev_async(void* host_ptr, vx_buffer_h hbuffer, uint64_t src_offset, uint64_t size, uint64_t* ticket) {
+  if (nullptr == hbuffer || nullptr == host_ptr || nullptr == ticket) return -1;
+  vx_buffer* b = as_buf(hbuffer);
+  if (src_offset + size > b->size) return -1;
+  vx_device* dev = b->dev;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  if (!dev->copy_stream) {
+    VX_CUDA_OK(cudaStreamCreateWithFlags(&dev->copy_stream, cudaStreamNonBlocking));
+    VX_CUDA_OK(cudaEventCreateWithFlags(&dev->copy_fork, cudaEventDisableTiming));
+    for (cudaEvent_t& e : dev->copy_done) VX_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  const uint64_t t = dev->copy_next_ticket;
+  if (t >= 16) VX_CUDA_OK(cudaEventSynchronize(dev->copy_done[t % 16]));  // the ring slot's previous copy
+  VX_CUDA_OK(cudaEventRecord(dev->copy_fork, dev->stream));
+  VX_CUDA_OK(cudaStreamWaitEvent(dev->copy_stream, dev->copy_fork, 0));
+  VX_CUDA_OK(cudaMemcpyAsync(host_ptr, (const char*)b->dptr + src_offset, size, cudaMemcpyDeviceToHost, dev->copy_stream));
+  VX_CUDA_OK(cudaEventRecord(dev->copy_done[t % 16], dev->copy_stream));
+  dev->copy_next_ticket = t + 1;
+  *ticket = t;
+  return 0;
+}
+
+int vx_cuda_copy_wait(vx_device_h hdevice, uint64_t ticket) {
+  if (nullptr == hdevice) return -1;
+  vx_device* dev = as_dev(hdevice);
+  if (!dev->copy_stream || ticket >= dev->copy_next_ticket) return -1;
+  if (ticket + 16 < dev->copy_next_ticket) return 0;  // its ring slot was reused, which waited for it
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  VX_CUDA_OK(cudaEventSynchronize(dev->copy_done[ticket % 16]));
   return 0;
 }
 

@@ -60,6 +60,11 @@ struct vx_device {
   cudaDeviceProp prop;
   cudaStream_t stream;
   cudaEvent_t ev_start, ev_stop;
+  // asynchronous read-back (vx_cuda_copy_from_dev_async): a second stream + a ring of completion events
+  cudaStream_t copy_stream;     // created by the first asynchronous copy
+  cudaEvent_t copy_fork;        // launch stream -> copy stream ordering
+  cudaEvent_t copy_done[16];
+  uint64_t copy_next_ticket;
   bool run_recorded;            // ev_start/ev_stop bracket the last vx_start
   std::map<uint32_t, uint32_t> dcrs;
   vx_buffer* buffers;           // intrusive list of live allocations

@@ -2,13 +2,42 @@
 the ranks, ONE gather of the per-rank strip buffers per frame.
 
 The reference is single-device (no collective anywhere in /root/reference); the nearest analogue is its
-striping of raster tiles over raster units (sim/simx/raster_unit.cpp:109-111).  torch.distributed is
-plumbing only: NCCL over NVLink on the GPU box, gloo in the CPU tests.
+striping of raster tiles over raster units (sim/simx/raster_unit.cpp:109-111).
+
+Product path: `NcclFrameGather` -- the C entry vx_cuda_frame_gather (csrc/vx_nccl.cu: NCCL send/receive group +
+one de-interleave kernel on the launch stream); torch.distributed only carries the 128-byte communicator id to
+the ranks at start-up, no torch op runs between vx_start and the host frame.
+`FrameGather` is the same assembly written with torch.distributed collectives: it runs on gloo, so the CPU tests
+(tests/test_multi_gloo.py) can check the row dealing / de-interleave logic with world_size 2 and 3.
 """
 import torch
 import torch.distributed as dist
 
 from .formats import rank_row_index, rank_rows
+
+
+class NcclFrameGather:
+    """One communicator per device; gather() enqueues the frame assembly behind the frame's kernels."""
+
+    def __init__(self, dev, width, height, rows_per_block, dst=0, group=None):
+        from . import vortex as vx
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        ident = [vx.comm_unique_id() if self.rank == dst else None]
+        dist.broadcast_object_list(ident, src=dst, group=group)  # start-up plumbing: 128 bytes
+        self.comm = vx.Comm(dev, ident[0], self.rank, self.world)
+        self.dev, self.w, self.h, self.rpb, self.dst = dev, width, height, rows_per_block, dst
+        self.frame = dev.alloc(height * width * 4) if self.rank == dst else None
+
+    def gather(self, strip_buf):
+        """strip_buf: this rank's vx Buffer.  Returns the root's frame Buffer (None elsewhere); asynchronous."""
+        self.comm.frame_gather(strip_buf, self.frame, self.w, self.h, self.rpb, self.dst)
+        return self.frame
+
+    def close(self):
+        self.comm.close()
+        if self.frame is not None:
+            self.frame.free()
+            self.frame = None
 
 
 class FrameGather:

@@ -49,7 +49,10 @@ EXPORTS = [
 ]
 CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx_cuda_host_unregister",
                 "vx_cuda_perf_totals", "vx_cuda_draw3d_binning", "vx_cuda_rt_build_lbvh",
-                "vx_cuda_rt_node4_image", "vx_cuda_fill32", "vx_cuda_probe_read_bandwidth"]  # include/vortex_cuda.h
+                "vx_cuda_rt_node4_image", "vx_cuda_fill32", "vx_cuda_probe_read_bandwidth",
+                "vx_cuda_comm_unique_id", "vx_cuda_comm_init", "vx_cuda_comm_destroy", "vx_cuda_frame_gather",
+                "vx_cuda_gather_bytes", "vx_cuda_copy_from_dev_async", "vx_cuda_copy_wait"]  # include/vortex_cuda.h
+VX_CUDA_COMM_ID_BYTES = 128
 
 _lib = None
 
@@ -90,6 +93,10 @@ def lib():
             "vx_cuda_rt_node4_image": [vp, vp, u64, C.POINTER(u64)],
             "vx_cuda_fill32": [vp, u64, u64, u32],
             "vx_cuda_probe_read_bandwidth": [vp, u64, u32, C.POINTER(C.c_float)],
+            "vx_cuda_copy_from_dev_async": [vp, vp, u64, u64, C.POINTER(u64)], "vx_cuda_copy_wait": [vp, u64],
+            "vx_cuda_comm_unique_id": [vp], "vx_cuda_comm_init": [vp, vp, u32, u32, C.POINTER(vp)],
+            "vx_cuda_comm_destroy": [vp], "vx_cuda_frame_gather": [vp, vp, vp, vp, u32, u32, u32, u32],
+            "vx_cuda_gather_bytes": [vp, vp, vp, u64, vp, C.POINTER(u64), C.POINTER(u64), u32],
             "vx_cuda_draw3d_binning": [vp, vp, u32, vp, u32, C.c_float, C.c_float, u32, u32, u32, u32, u32, u32,
                                        C.POINTER(vp), C.POINTER(vp), vp],
         }
@@ -143,6 +150,13 @@ class Buffer:
         _check(lib().vx_copy_from_dev(p, self.handle, offset, n), "vx_copy_from_dev")
         return dst
 
+    def read_async(self, dst, offset=0):
+        """vx_cuda_copy_from_dev_async: returns a ticket for Device.copy_wait (dst should be pinned)."""
+        p, n = _host_ptr(dst)
+        t = C.c_uint64()
+        _check(lib().vx_cuda_copy_from_dev_async(p, self.handle, offset, n, C.byref(t)), "vx_cuda_copy_from_dev_async")
+        return t.value
+
     def fill32(self, value, offset=0, size=None):
         """Device-side fill with a 32-bit pattern (vx_cuda_fill32)."""
         _check(lib().vx_cuda_fill32(self.handle, offset, self.size - offset if size is None else size, value), "vx_cuda_fill32")
@@ -150,6 +164,42 @@ class Buffer:
     def free(self):
         if self.handle is not None:
             _check(lib().vx_mem_free(self.handle), "vx_mem_free")
+            self.handle = None
+
+
+def comm_unique_id():
+    """VX_CUDA_COMM_ID_BYTES bytes naming a new communicator (vx_cuda_comm_unique_id): make it on one rank, hand it
+    to the others."""
+    buf = (C.c_ubyte * VX_CUDA_COMM_ID_BYTES)()
+    _check(lib().vx_cuda_comm_unique_id(buf), "vx_cuda_comm_unique_id")
+    return bytes(buf)
+
+
+class Comm:
+    """This device's membership in a group of num_ranks devices (vx_cuda_comm_init; collective)."""
+
+    def __init__(self, dev, comm_id, rank, num_ranks):
+        assert len(comm_id) == VX_CUDA_COMM_ID_BYTES
+        h = C.c_void_p()
+        idbuf = (C.c_ubyte * VX_CUDA_COMM_ID_BYTES).from_buffer_copy(comm_id)
+        _check(lib().vx_cuda_comm_init(dev.handle, idbuf, rank, num_ranks, C.byref(h)), "vx_cuda_comm_init")
+        self.dev, self.handle, self.rank, self.num_ranks = dev, h, rank, num_ranks
+
+    def frame_gather(self, strip, frame, width, height, rows_per_block, root=0):
+        """Asynchronous on the launch stream: strips -> the root's `frame` buffer (None on the other ranks)."""
+        _check(lib().vx_cuda_frame_gather(self.dev.handle, self.handle, strip.handle, frame.handle if frame else None,
+                                          width, height, rows_per_block, root), "vx_cuda_frame_gather")
+
+    def gather_bytes(self, src, nbytes, dst=None, offsets=None, sizes=None, root=0):
+        n = self.num_ranks
+        off = (C.c_uint64 * n)(*offsets) if offsets is not None else None
+        siz = (C.c_uint64 * n)(*sizes) if sizes is not None else None
+        _check(lib().vx_cuda_gather_bytes(self.dev.handle, self.handle, src.handle, nbytes, dst.handle if dst else None,
+                                          off, siz, root), "vx_cuda_gather_bytes")
+
+    def close(self):
+        if self.handle is not None:
+            lib().vx_cuda_comm_destroy(self.handle)
             self.handle = None
 
 
@@ -199,6 +249,9 @@ class Device:
 
     def ready_wait(self, timeout_ms=VX_MAX_TIMEOUT):
         _check(lib().vx_ready_wait(self.handle, timeout_ms), "vx_ready_wait")
+
+    def copy_wait(self, ticket):
+        _check(lib().vx_cuda_copy_wait(self.handle, ticket), "vx_cuda_copy_wait")
 
     def dcr_write(self, addr, value):
         _check(lib().vx_dcr_write(self.handle, addr, value), "vx_dcr_write")
