@@ -205,11 +205,17 @@ def roofline_record(args, wl, r, dev, tracer, vx, cpu):
     pi = profile_inputs(args, args.workload)
     rec["issue"] = {"peak_warp_inst_per_s": issue_peak, "sm_mhz": sm_mhz}
     if pi:
-        rec["traffic"] = pi.get("dram_bytes")
+        part = pi.get("step_fraction", 1.0)  # the capture covers this share of the bench step (c5: 16 Mi of 64 Mi rays)
+        rec["traffic"] = int(pi["dram_bytes"] / part) if pi.get("dram_bytes") is not None else None
         rec["issue"].update(issue_active=pi.get("issue_active"), lanes_per_inst=pi.get("lanes_per_inst"),
-                            warp_inst_per_step=pi.get("warp_inst"), source=pi.get("source"))
+                            warp_inst_per_step=int(pi["warp_inst"] / part) if pi.get("warp_inst") else None,
+                            source=pi.get("source"), capture_note=pi.get("partial"))
         if pi.get("warp_inst"):
-            rec["issue"]["frac"] = pi["warp_inst"] / kern_s / issue_peak
+            # share of the issue slots of the step that carried an instruction, and the share that carried useful
+            # lanes: the two factors of the issue roofline
+            rec["issue"]["frac"] = pi["warp_inst"] / part / kern_s / issue_peak
+            if pi.get("lanes_per_inst"):
+                rec["issue"]["lane_weighted_frac"] = rec["issue"]["frac"] * pi["lanes_per_inst"] / 32.0
     else:
         rec["traffic"] = None
     return rec

@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--frames", type=int, default=3)
     ap.add_argument("--tune", type=int, default=0)
     ap.add_argument("--stats", type=int, default=0)
+    ap.add_argument("--chains", type=int, default=0, help="VX_DCR_RT_CHAINS (0 = default)")
     ap.add_argument("--builder", default="host", choices=["host", "device"])
     ap.add_argument("--rays", type=int, default=None)
     ap.add_argument("--ranks", type=int, default=1, help="render rank 0's strip of a frame split over this many ranks")
@@ -42,6 +43,7 @@ def main():
     dev.dcr_write(vx.VX_DCR_RT_VARIANT, args.variant)
     dev.dcr_write(vx.VX_DCR_RT_KEEP_ACTIVE, args.tune)
     dev.dcr_write(vx.VX_DCR_RT_STATS, args.stats)
+    dev.dcr_write(vx.VX_DCR_RT_CHAINS, args.chains)
     times = []
     if "rays" in cfg:
         n = args.rays or cfg["rays"]

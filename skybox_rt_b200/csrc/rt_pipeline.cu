@@ -34,6 +34,8 @@ struct WideCache {
   bool valid;
 };
 
+constexpr int kMaxChains = 4;
+
 struct RtState {
   unsigned long long* d_counters;  // CTR_COUNT u64, zeroed at every launch
   WideCache wide;
@@ -48,6 +50,9 @@ struct RtState {
   char* d_wave;
   uint64_t wave_jobs;
   WaveBufs wave;
+  WaveCtl* d_wave_ctl;             // kMaxChains control blocks
+  cudaStream_t chain_stream[3];    // the extra chains of a frame run here (the first one on the device stream)
+  cudaEvent_t chain_fork, chain_join[3];
   int wave_blocks_per_sm[18];      // occupancy per (stage, scheduler, stats) instantiation
 };
 
@@ -56,6 +61,12 @@ static int rt_state(vx_device* dev, RtState** out) {
     RtState* s = new RtState();
     memset(s, 0, sizeof(*s));
     VX_CUDA_OK(cudaMalloc(&s->d_counters, sizeof(unsigned long long) * CTR_COUNT));
+    VX_CUDA_OK(cudaMalloc(&s->d_wave_ctl, sizeof(WaveCtl) * kMaxChains));
+    VX_CUDA_OK(cudaEventCreateWithFlags(&s->chain_fork, cudaEventDisableTiming));
+    for (int i = 0; i < kMaxChains - 1; ++i) {
+      VX_CUDA_OK(cudaStreamCreateWithFlags(&s->chain_stream[i], cudaStreamNonBlocking));
+      VX_CUDA_OK(cudaEventCreateWithFlags(&s->chain_join[i], cudaEventDisableTiming));
+    }
     dev->rt = s;
   }
   *out = dev->rt;
@@ -188,7 +199,7 @@ static int wave_reserve(RtState* st, uint64_t jobs, bool need_sum) {
   st->d_wave = nullptr;
   st->wave_jobs = 0;
   const size_t n = (size_t)jobs;
-  const size_t sz_ctl = align256(sizeof(WaveCtl)), sz_hit = align256(n * sizeof(uint2)), sz_path = align256(n * sizeof(float4)),
+  const size_t sz_ctl = 0, sz_hit = align256(n * sizeof(uint2)), sz_path = align256(n * sizeof(float4)),
                sz_q = align256(n * 2 * sizeof(float4)), sz_sum = need_sum ? align256(n * sizeof(float4)) : 0;
   const size_t total = sz_ctl + 2 * sz_hit + sz_path + 2 * sz_q + sz_sum;
   if (cudaMalloc(&st->d_wave, total) != cudaSuccess) {
@@ -197,7 +208,8 @@ static int wave_reserve(RtState* st, uint64_t jobs, bool need_sum) {
     return -1;
   }
   char* p = st->d_wave;
-  st->wave.ctl = reinterpret_cast<WaveCtl*>(p); p += sz_ctl;
+  st->wave.ctl = st->d_wave_ctl;
+  st->wave.job_base = 0;
   st->wave.hit1 = reinterpret_cast<uint2*>(p); p += sz_hit;
   st->wave.hit2 = reinterpret_cast<uint2*>(p); p += sz_hit;
   st->wave.path = reinterpret_cast<float4*>(p); p += sz_path;
@@ -209,8 +221,8 @@ static int wave_reserve(RtState* st, uint64_t jobs, bool need_sum) {
 }
 
 template <int STAGE, int SCHED, bool STATS>
-static int wave_trace(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, uint32_t rows,
-                      uint32_t jobs, uint32_t s) {
+static int wave_trace(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, const WaveBufs& wb,
+                      cudaStream_t stream, uint32_t rows, uint32_t jobs, uint32_t s) {
   const size_t smem = sizeof(uint2) * kSmStack * kWideThreads;
   int* occ = st->wave_blocks_per_sm + (STAGE * 6 + SCHED * 2 + (STATS ? 1 : 0));
   auto kernel = rt_wave_trace_kernel<STAGE, SCHED, STATS>;
@@ -227,33 +239,73 @@ static int wave_trace(vx_device* dev, RtState* st, const kernel_arg_t& a, const 
     const uint64_t need = ((uint64_t)jobs + kWideThreads - 1) / kWideThreads;
     if (need < grid) grid = need;
   }
-  kernel<<<(unsigned)grid, kWideThreads, smem, dev->stream>>>(a, sc, st->wave, rows, jobs, s, st->d_counters);
+  kernel<<<(unsigned)grid, kWideThreads, smem, stream>>>(a, sc, wb, rows, jobs, s, st->d_counters);
   return 0;
 }
 
+// One sample plane of one chain: the six launches of rt_wave.cuh for the jobs [wb.job_base, wb.job_base + jobs).
 template <int SCHED, bool STATS>
-static int wave_frame(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, uint32_t rows,
-                      uint32_t jobs, uint32_t* launches) {
-  cudaStream_t s = dev->stream;
+static int wave_chain(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, const WaveBufs& wb,
+                      cudaStream_t s, uint32_t rows, uint32_t jobs, uint32_t sample, uint32_t* launches) {
   const float4* tris = sc.tris;
   const unsigned blocks = (jobs + 255u) / 256u;
   const unsigned sm_blocks = (unsigned)dev->prop.multiProcessorCount * 8u;
-  VX_CUDA_OK(cudaMemsetAsync(st->wave.ctl, 0, sizeof(WaveCtl), s));
-  for (uint32_t sample = 0; sample < a.spp; ++sample) {
-    if (wave_trace<0, SCHED, STATS>(dev, st, a, sc, rows, jobs, sample) != 0) return -1;
-    rt_wave_shade1_kernel<<<blocks, 256, 0, s>>>(a, tris, st->wave, rows, jobs, sample);
-    *launches += 2;
-    if (a.mode >= SRT_MODE_SHADOW) {
-      if (wave_trace<1, SCHED, STATS>(dev, st, a, sc, rows, jobs, sample) != 0) return -1;
-      *launches += 1;
-    }
-    if (a.mode >= SRT_MODE_BOUNCE) {
-      rt_wave_shade2_kernel<<<blocks < sm_blocks ? blocks : sm_blocks, 256, 0, s>>>(a, tris, st->wave);
-      if (wave_trace<2, SCHED, STATS>(dev, st, a, sc, rows, jobs, sample) != 0) return -1;
-      *launches += 2;
-    }
-    rt_wave_combine_kernel<<<blocks, 256, 0, s>>>(a, st->wave, rows, jobs, sample, st->d_counters);
+  if (wave_trace<0, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, sample) != 0) return -1;
+  rt_wave_shade1_kernel<<<blocks, 256, 0, s>>>(a, tris, wb, rows, jobs, sample);
+  *launches += 2;
+  if (a.mode >= SRT_MODE_SHADOW) {
+    if (wave_trace<1, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, sample) != 0) return -1;
     *launches += 1;
+  }
+  if (a.mode >= SRT_MODE_BOUNCE) {
+    rt_wave_shade2_kernel<<<blocks < sm_blocks ? blocks : sm_blocks, 256, 0, s>>>(a, tris, wb);
+    if (wave_trace<2, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, sample) != 0) return -1;
+    *launches += 2;
+  }
+  rt_wave_combine_kernel<<<blocks, 256, 0, s>>>(a, wb, rows, jobs, sample, st->d_counters);
+  *launches += 1;
+  return 0;
+}
+
+// A frame = `chains` independent chains over disjoint job ranges (whole 256-job groups, so that the shading CTAs
+// of different chains never share a tile), each on its own stream.  Every trace kernel is persistent and ends with
+// a tail in which a few long rays keep a few warps busy (ncu: K5 of C3 ran at 30 % warps active); with two chains
+// the other chain's next kernel moves into the SM slots a tail frees, so the tails overlap useful work instead of
+// idling the GPU.  The chains share hit1 / path / sum (indexed by frame-wide job id) and split the queues; each
+// has its own control block.  Joined on the device stream before vx_start's closing event.
+template <int SCHED, bool STATS>
+static int wave_frame(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, uint32_t rows,
+                      uint32_t jobs, uint32_t chains, uint32_t* launches) {
+  cudaStream_t s0 = dev->stream;
+  const uint32_t groups = (jobs + 255u) / 256u;
+  if (chains > groups) chains = groups;
+  if (chains < 1u) chains = 1u;
+  VX_CUDA_OK(cudaMemsetAsync(st->d_wave_ctl, 0, sizeof(WaveCtl) * kMaxChains, s0));
+  if (chains > 1u) {
+    VX_CUDA_OK(cudaEventRecord(st->chain_fork, s0));
+    for (uint32_t c = 1; c < chains; ++c) VX_CUDA_OK(cudaStreamWaitEvent(st->chain_stream[c - 1], st->chain_fork, 0));
+  }
+  WaveBufs wb[kMaxChains];
+  uint32_t n_jobs[kMaxChains];
+  for (uint32_t c = 0; c < chains; ++c) {
+    const uint32_t g0 = (uint32_t)((uint64_t)groups * c / chains), g1 = (uint32_t)((uint64_t)groups * (c + 1) / chains);
+    const uint32_t first = g0 * 256u, last = g1 * 256u < jobs ? g1 * 256u : jobs;
+    wb[c] = st->wave;
+    wb[c].job_base = first;
+    wb[c].ctl = st->d_wave_ctl + c;
+    wb[c].q_shadow = st->wave.q_shadow + 2 * (size_t)first;  // a chain queues at most one shadow / bounce ray per job
+    wb[c].q_bounce = st->wave.q_bounce + 2 * (size_t)first;
+    wb[c].hit2 = st->wave.hit2 + first;
+    n_jobs[c] = last - first;
+  }
+  for (uint32_t sample = 0; sample < a.spp; ++sample)
+    for (uint32_t c = 0; c < chains; ++c)
+      if (wave_chain<SCHED, STATS>(dev, st, a, sc, wb[c], c == 0 ? s0 : st->chain_stream[c - 1], rows, n_jobs[c], sample,
+                                   launches) != 0)
+        return -1;
+  for (uint32_t c = 1; c < chains; ++c) {
+    VX_CUDA_OK(cudaEventRecord(st->chain_join[c - 1], st->chain_stream[c - 1]));
+    VX_CUDA_OK(cudaStreamWaitEvent(s0, st->chain_join[c - 1], 0));
   }
   return 0;
 }
@@ -261,6 +313,12 @@ static int wave_frame(vx_device* dev, RtState* st, const kernel_arg_t& a, const 
 void rt_destroy(vx_device* dev) {
   if (!dev->rt) return;
   cudaFree(dev->rt->d_counters);
+  cudaFree(dev->rt->d_wave_ctl);
+  cudaEventDestroy(dev->rt->chain_fork);
+  for (int i = 0; i < kMaxChains - 1; ++i) {
+    cudaStreamDestroy(dev->rt->chain_stream[i]);
+    cudaEventDestroy(dev->rt->chain_join[i]);
+  }
   if (dev->rt->wide.d_nodes4) cudaFree(dev->rt->wide.d_nodes4);
   if (dev->rt->d_spill) cudaFree(dev->rt->d_spill);
   if (dev->rt->d_samples) cudaFree(dev->rt->d_samples);
@@ -435,12 +493,15 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
     if (wave_reserve(st, jobs, a.spp > 1) != 0) return -1;
     uint32_t n = 0;
     int rc;
-    if (sched == SCHED_WHILE) rc = stats ? wave_frame<SCHED_WHILE, true>(dev, st, a, sc, rows, (uint32_t)jobs, &n)
-                                         : wave_frame<SCHED_WHILE, false>(dev, st, a, sc, rows, (uint32_t)jobs, &n);
-    else if (sched == SCHED_DEFER) rc = stats ? wave_frame<SCHED_DEFER, true>(dev, st, a, sc, rows, (uint32_t)jobs, &n)
-                                              : wave_frame<SCHED_DEFER, false>(dev, st, a, sc, rows, (uint32_t)jobs, &n);
-    else rc = stats ? wave_frame<SCHED_VOTE, true>(dev, st, a, sc, rows, (uint32_t)jobs, &n)
-                    : wave_frame<SCHED_VOTE, false>(dev, st, a, sc, rows, (uint32_t)jobs, &n);
+    uint32_t chains = vx_dev_dcr(dev, VX_DCR_RT_CHAINS);
+    if (chains == 0u) chains = jobs >= (1u << 18) ? 2u : 1u;  // small frames are launch-bound: one chain
+    if (chains > (uint32_t)kMaxChains) chains = kMaxChains;
+    if (sched == SCHED_WHILE) rc = stats ? wave_frame<SCHED_WHILE, true>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n)
+                                         : wave_frame<SCHED_WHILE, false>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n);
+    else if (sched == SCHED_DEFER) rc = stats ? wave_frame<SCHED_DEFER, true>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n)
+                                              : wave_frame<SCHED_DEFER, false>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n);
+    else rc = stats ? wave_frame<SCHED_VOTE, true>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n)
+                    : wave_frame<SCHED_VOTE, false>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n);
     if (rc != 0) return -1;
     VX_CUDA_OK(cudaGetLastError());
     dev->last_launches = n + extra_launches;

@@ -40,6 +40,7 @@ struct WaveCtl {
 
 // Internal ray record, 32 B: (o.xyz, job | d.xyz, tmax); tmin = 0 for every generated ray.
 struct WaveBufs {
+  uint32_t job_base; // first job of this chain (a frame may run as several independent chains, rt_pipeline.cu)
   WaveCtl* ctl;
   uint2* hit1;      // [jobs]  (t, triangle record) of the primary ray; record = SRT_MISS when nothing was hit
   float4* path;     // [jobs]  (albedo1 bits, n.l at hit 1 or 0, albedo2 bits | kBounceMissed, n.l at hit 2 or 0)
@@ -126,7 +127,8 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
       my_job = job;
       if (STAGE == 0) {
         uint32_t x, ly;
-        if (job_pixel(job, W, rows, tiles_x, x, ly)) {
+        my_job = job + wb.job_base;  // hit1 / path are indexed by the frame-wide job id
+        if (job_pixel(my_job, W, rows, tiles_x, x, ly)) {
           have_job = true;
           if (STATS) stats.rays += 1;
           ray_setup(r, cam.eye, wave_camera_dir(a, cam, seed_hash, x, global_row(a, ly), s), 0.0f, false);
@@ -158,10 +160,10 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
 __global__ void __launch_bounds__(256)
 rt_wave_shade1_kernel(const __grid_constant__ kernel_arg_t a, const float4* __restrict__ tris, const WaveBufs wb,
                       uint32_t rows, uint32_t cam_jobs, uint32_t s) {
-  const uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x, job = wb.job_base + local;
   const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
   uint32_t x = 0, ly = 0;
-  const bool live = job < cam_jobs && job_pixel(job, W, rows, tiles_x, x, ly);
+  const bool live = local < cam_jobs && job_pixel(job, W, rows, tiles_x, x, ly);
   bool want_shadow = false, want_bounce = false;
   float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0, b0 = s0, b1 = s0;
   if (live) {
@@ -257,10 +259,10 @@ rt_wave_shade2_kernel(const __grid_constant__ kernel_arg_t a, const float4* __re
 __global__ void __launch_bounds__(256)
 rt_wave_combine_kernel(const __grid_constant__ kernel_arg_t a, const WaveBufs wb, uint32_t rows, uint32_t cam_jobs,
                        uint32_t s, unsigned long long* counters) {
-  const uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x, job = wb.job_base + local;
   const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
   uint32_t x = 0, ly = 0;
-  if (job < cam_jobs && job_pixel(job, W, rows, tiles_x, x, ly)) {
+  if (local < cam_jobs && job_pixel(job, W, rows, tiles_x, x, ly)) {
     V3 rad = ld3(a.sky);
     const uint2 h = wb.hit1[job];
     if (h.y != SRT_MISS) {

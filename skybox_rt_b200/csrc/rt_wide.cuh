@@ -93,6 +93,21 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
   return v;
 }
 
+// 32-byte read-only load (ld.global.nc.v8.f32 -> LDG.E.256.CONSTANT on sm_100; p must be 32-byte aligned).
+struct F8 {
+  float4 a, b;
+};
+__device__ __forceinline__ F8 ldg256(const float4* p) {
+  F8 r;
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.a.x), "=f"(r.a.y), "=f"(r.a.z), "=f"(r.a.w), "=f"(r.b.x), "=f"(r.b.y), "=f"(r.b.z), "=f"(r.b.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float4 sel4(bool c, const float4 a, const float4 b) {
+  return make_float4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w);
+}
+
 // One traversal stack per thread: shared entries first ([entry][thread]), local spill above.  The spill
 // array is a separate kernel-local array (passed by pointer) so that `top` and `base` stay in registers.
 // The stack pointer IS the shared-space byte address of the next free entry (entries of one thread lie
@@ -138,11 +153,24 @@ template <bool STATS>
 __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const RayState& r, float best_t, Stack& st,
                                           Stats& stats) {
   // float4 index of the node's first plane, kept in 32 bits (the host refuses images of 2^32 float4 = 64 GiB):
-  // every load address is one 32-bit add / xor and one widening multiply-add onto the uniform base pointer
+  // every load address is one 32-bit add and one widening multiply-add onto the uniform base pointer.
   const uint32_t n0 = cu.ref * 8u;
+#ifdef SRT_NODE_LDG128
+  // seven 16-byte loads, near / far plane picked by address from the ray octant (the round-1 form, kept for A/B)
   const float4 nx = __ldg(sc.nodes + (n0 + r.ox)), fx = __ldg(sc.nodes + ((n0 + r.ox) ^ 1u));
   const float4 ny = __ldg(sc.nodes + (n0 + r.oy)), fy = __ldg(sc.nodes + ((n0 + r.oy) ^ 1u));
   const float4 nz = __ldg(sc.nodes + (n0 + r.oz)), fz = __ldg(sc.nodes + ((n0 + r.oz) ^ 1u));
+#else
+  // Three 32-byte loads (LDG.E.256, sm_100) bring the lo / hi plane pair of one axis each.  ncu on the 16-byte
+  // form: l1tex data-pipe wavefronts at 80 % of peak in the shadow + bounce trace kernel -- every load instruction
+  // costs one L1 wavefront per DISTINCT node line among the warp's lanes, so a node visit cost seven; now four.
+  // The near / far pick by ray octant moves from the address into 24 selects.
+  const F8 px = ldg256(sc.nodes + n0), py = ldg256(sc.nodes + (n0 + 2u)), pz = ldg256(sc.nodes + (n0 + 4u));
+  const bool sx = r.ox != 0u, sy = r.oy != 2u, sz = r.oz != 4u;  // near plane = hi plane on that axis
+  const float4 nx = sel4(sx, px.b, px.a), fx = sel4(sx, px.a, px.b);
+  const float4 ny = sel4(sy, py.b, py.a), fy = sel4(sy, py.a, py.b);
+  const float4 nz = sel4(sz, pz.b, pz.a), fz = sel4(sz, pz.a, pz.b);
+#endif
   const float4 rf = __ldg(sc.nodes + (n0 + 6u));
   if (STATS) { stats.nodes += 1; if (step_leader()) stats.wnode += 1; }
 #define SRT_CHILD(c, tn, hit)                                                                              \

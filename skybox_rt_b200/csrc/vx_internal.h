@@ -106,6 +106,9 @@ struct vx_device {
 #define VX_DCR_RT_PREFETCH 0x803 /* 1 = warm L2 with the scene before tracing when it fits (measured: no gain, off by default) */
 #define VX_DCR_RT_SPLIT_SAMPLES 0x807 /* multi-sample frames as (pixel, sample) jobs + ordered resolve: 0 = when spp > 1,
                                         1 = never (a pixel's samples run sequentially in one lane), 2 = always */
+#define VX_DCR_RT_CHAINS  0x809 /* wavefront pipeline: independent chains a frame is split into so that the tail of one
+                                   chain's trace kernel overlaps the other chain's next kernel (0 = default: 2 for
+                                   frames of >= 2^18 jobs, else 1; 1..4 forced)                                      */
 #define VX_DCR_RT_REPACK  0x808 /* BVH2 -> Node4: 0 = on the device (rt_repack_device.cu), 1 = on the host (rt_repack.cpp), A/B */
 #define VX_DCR_RT_END     0x810
 

@@ -61,6 +61,24 @@ def test_terrain_frames_match_oracle(terrain, variant, w, h, mode, spp):
     assert ray_counts(tracer.counters()) == ray_counts(ctr)
 
 
+@pytest.mark.parametrize("chains", [1, 2, 3, 4])
+@pytest.mark.parametrize("w,h,mode,spp", [(320, 180, 2, 1), (201, 97, 2, 3), (64, 33, 1, 1), (7, 5, 0, 2), (40, 24, 2, 1)])
+def test_wavefront_chains_do_not_change_the_frame(terrain, chains, w, h, mode, spp):
+    """VX_DCR_RT_CHAINS splits a frame into independent chains on separate streams (tail overlap); 0 picks 2 only for
+    large frames, so the split is forced here on small ones, including frames with fewer 256-job groups than chains."""
+    tracer, (onodes, otris), _ = terrain
+    tracer.dev.dcr_write(vx.VX_DCR_RT_VARIANT, vx.RT_VARIANT_WAVE)
+    tracer.dev.dcr_write(vx.VX_DCR_RT_CHAINS, chains)
+    try:
+        fb = tracer.render(rt.make_arg(w, h, mode, spp=spp, seed=99, scene="terrain"))
+        c = tracer.counters()
+    finally:
+        tracer.dev.dcr_write(vx.VX_DCR_RT_CHAINS, 0)
+    ref, ctr = o.render(o.make_arg(w, h, mode, spp=spp, seed=99, scene="terrain"), onodes, otris)
+    assert np.array_equal(fb, ref), f"{(fb != ref).sum()} of {fb.size} pixels differ"
+    assert ray_counts(c) == ray_counts(ctr)
+
+
 @pytest.mark.parametrize("variant", VARIANTS)
 def test_explicit_rays_hit_records_bit_exact(terrain, variant):
     tracer, (onodes, otris), soup = terrain
