@@ -150,7 +150,8 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
       }
     }
   };
-  run_warp<SCHED, STATS>(sc, cu, r, best, st, stats, pool, have_job, advance);
+  // camera rays are coherent (ALU-bound): 16-byte loads; shadow / bounce rays (L1-bound): 32-byte loads
+  run_warp<SCHED, STATS, STAGE != 0>(sc, cu, r, best, st, stats, pool, have_job, advance);
   if (STATS) flush_stats(stats, counters);
 }
 

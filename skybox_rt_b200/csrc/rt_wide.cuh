@@ -149,28 +149,31 @@ __device__ __forceinline__ uint32_t pop_next(Stack& st, float best_t) {
 // ---- NODE step: test the four children, continue with the nearest, push the others ---------------
 // Box test per child: entry = max(near planes, tmin), exit = min(far planes, best_t); the child
 // is visited when entry <= exit * kPad.  Boxes were inflated by the scene delta at repack time.
-template <bool STATS>
+template <bool STATS, bool LD256>
 __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const RayState& r, float best_t, Stack& st,
                                           Stats& stats) {
   // float4 index of the node's first plane, kept in 32 bits (the host refuses images of 2^32 float4 = 64 GiB):
   // every load address is one 32-bit add and one widening multiply-add onto the uniform base pointer.
   const uint32_t n0 = cu.ref * 8u;
-#ifdef SRT_NODE_LDG128
-  // seven 16-byte loads, near / far plane picked by address from the ray octant (the round-1 form, kept for A/B)
-  const float4 nx = __ldg(sc.nodes + (n0 + r.ox)), fx = __ldg(sc.nodes + ((n0 + r.ox) ^ 1u));
-  const float4 ny = __ldg(sc.nodes + (n0 + r.oy)), fy = __ldg(sc.nodes + ((n0 + r.oy) ^ 1u));
-  const float4 nz = __ldg(sc.nodes + (n0 + r.oz)), fz = __ldg(sc.nodes + ((n0 + r.oz) ^ 1u));
-#else
-  // Three 32-byte loads (LDG.E.256, sm_100) bring the lo / hi plane pair of one axis each.  ncu on the 16-byte
-  // form: l1tex data-pipe wavefronts at 80 % of peak in the shadow + bounce trace kernel -- every load instruction
-  // costs one L1 wavefront per DISTINCT node line among the warp's lanes, so a node visit cost seven; now four.
-  // The near / far pick by ray octant moves from the address into 24 selects.
-  const F8 px = ldg256(sc.nodes + n0), py = ldg256(sc.nodes + (n0 + 2u)), pz = ldg256(sc.nodes + (n0 + 4u));
-  const bool sx = r.ox != 0u, sy = r.oy != 2u, sz = r.oz != 4u;  // near plane = hi plane on that axis
-  const float4 nx = sel4(sx, px.b, px.a), fx = sel4(sx, px.a, px.b);
-  const float4 ny = sel4(sy, py.b, py.a), fy = sel4(sy, py.a, py.b);
-  const float4 nz = sel4(sz, pz.b, pz.a), fz = sel4(sz, pz.a, pz.b);
-#endif
+  // Two forms of the plane fetch, chosen per kernel (LD256):
+  //  * six 16-byte loads, near / far plane picked by ADDRESS from the ray octant: no extra arithmetic, but every load
+  //    instruction costs L1 data-pipe wavefronts for each distinct node line among the warp's lanes;
+  //  * three 32-byte loads (LDG.E.256, sm_100), one per axis, near / far picked by 24 selects on the ALU pipe.
+  // Measured: coherent rays (camera rays, C2) are bound by the ALU pipe and lose 6 % to the
+  // selects; the shadow + bounce kernels run the L1 data pipe at 80 % of peak and gain 3-4 % from the wide loads;
+  // the HBM-resident random-ray list (C5) loses 12 %.
+  float4 nx, fx, ny, fy, nz, fz;
+  if (LD256) {
+    const F8 px = ldg256(sc.nodes + n0), py = ldg256(sc.nodes + (n0 + 2u)), pz = ldg256(sc.nodes + (n0 + 4u));
+    const bool sx = r.ox != 0u, sy = r.oy != 2u, sz = r.oz != 4u;  // near plane = hi plane on that axis
+    nx = sel4(sx, px.b, px.a); fx = sel4(sx, px.a, px.b);
+    ny = sel4(sy, py.b, py.a); fy = sel4(sy, py.a, py.b);
+    nz = sel4(sz, pz.b, pz.a); fz = sel4(sz, pz.a, pz.b);
+  } else {
+    nx = __ldg(sc.nodes + (n0 + r.ox)); fx = __ldg(sc.nodes + ((n0 + r.ox) ^ 1u));
+    ny = __ldg(sc.nodes + (n0 + r.oy)); fy = __ldg(sc.nodes + ((n0 + r.oy) ^ 1u));
+    nz = __ldg(sc.nodes + (n0 + r.oz)); fz = __ldg(sc.nodes + ((n0 + r.oz) ^ 1u));
+  }
   const float4 rf = __ldg(sc.nodes + (n0 + 6u));
   if (STATS) { stats.nodes += 1; if (step_leader()) stats.wnode += 1; }
 #define SRT_CHILD(c, tn, hit)                                                                              \
@@ -292,7 +295,7 @@ __device__ __forceinline__ uint32_t take_jobs(Pool& p, bool want, unsigned long 
 // ---- the warp scheduler ----------------------------------------------------------------------------
 // advance(): warp-convergent; for every lane whose ray has ended it finishes / continues the lane's
 // job, then hands new jobs to lanes without one (sets have_job, cu, r, best).
-template <int SCHED, bool STATS, class Advance>
+template <int SCHED, bool STATS, bool LD256, class Advance>
 __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RayState& r, Hit& best, Stack& st,
                                          Stats& stats, const Pool& pool, const bool& have_job, Advance advance) {
   if (SCHED == SCHED_WHILE) {
@@ -307,7 +310,7 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
       if (pool.dry && !__any_sync(0xffffffffu, have_job)) return;
       for (;;) {
         while (cu.wants_node()) {
-          node_step<STATS>(sc, cu, r, best.t, st, stats);
+          node_step<STATS, LD256>(sc, cu, r, best.t, st, stats);
           if (pend == kNone && cu.wants_tri()) {
             pend = cu.ref;
             cu.go(pop_next(st, best.t));
@@ -329,7 +332,7 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
       advance();
       if (pool.dry && !__any_sync(0xffffffffu, have_job)) return;
       for (;;) {
-        while (cu.wants_node()) node_step<STATS>(sc, cu, r, best.t, st, stats);
+        while (cu.wants_node()) node_step<STATS, LD256>(sc, cu, r, best.t, st, stats);
         while (cu.wants_tri()) tri_step<STATS>(sc, cu, r, best, st, stats);
         if (__popc(__ballot_sync(0xffffffffu, cu.busy())) < sc.tune) break;
       }
@@ -368,7 +371,7 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
           pend = kNone;
         }
       } else {
-        if (wn) node_step<STATS>(sc, cu, r, best.t, st, stats);
+        if (wn) node_step<STATS, LD256>(sc, cu, r, best.t, st, stats);
       }
     }
   } else {
@@ -384,7 +387,7 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
       } else if (__popc(mt) >= ((sc.tune >> 8) & 0xff) || mn == 0u) {
         if (wt) tri_step<STATS>(sc, cu, r, best, st, stats);
       } else {
-        if (wn) node_step<STATS>(sc, cu, r, best.t, st, stats);
+        if (wn) node_step<STATS, LD256>(sc, cu, r, best.t, st, stats);
       }
     }
   }
@@ -545,7 +548,7 @@ __device__ __forceinline__ void wide_render_body(const kernel_arg_t& a, const Wi
     }
   };
 
-  run_warp<SCHED, STATS>(sc, cu, r, best, st, stats, pool, have_job, advance);
+  run_warp<SCHED, STATS, false>(sc, cu, r, best, st, stats, pool, have_job, advance);
 
   n_shadow = __reduce_add_sync(0xffffffffu, n_shadow);
   n_bounce = __reduce_add_sync(0xffffffffu, n_bounce);
@@ -625,7 +628,7 @@ rt_wide_rays_kernel(const float4* __restrict__ rays, float4* __restrict__ hits, 
     }
   };
 
-  run_warp<SCHED, STATS>(sc, cu, r, best, st, stats, pool, have_job, advance);
+  run_warp<SCHED, STATS, false>(sc, cu, r, best, st, stats, pool, have_job, advance);  // HBM-resident lists: 16-byte loads
   if (STATS) flush_stats(stats, counters);
 }
 
