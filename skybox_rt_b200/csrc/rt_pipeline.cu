@@ -48,7 +48,7 @@ struct RtState {
   size_t samples_capacity;         // in float4
   // wavefront pipeline (rt_wave.cuh): queues and path state for `wave_jobs` jobs, one allocation
   char* d_wave;
-  uint64_t wave_jobs;
+  uint64_t wave_jobs, wave_sum_jobs;
   WaveBufs wave;
   WaveCtl* d_wave_ctl;             // kMaxChains control blocks
   cudaStream_t chain_stream[3];    // the extra chains of a frame run here (the first one on the device stream)
@@ -193,14 +193,16 @@ void rt_buffer_freed(vx_device* dev, const vx_buffer* b) {
 // ---- wavefront pipeline (variants 4 / 5, rt_wave.cuh) ------------------------------------------------------------
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
-static int wave_reserve(RtState* st, uint64_t jobs, bool need_sum) {
-  if (st->d_wave && st->wave_jobs >= jobs && (!need_sum || st->wave.sum)) return 0;
+// queues and path state for `jobs` jobs of one pass; sum_jobs != 0: plus a per-pixel running sum between passes
+static int wave_reserve(RtState* st, uint64_t jobs, uint64_t sum_jobs) {
+  const bool need_sum = sum_jobs != 0;
+  if (st->d_wave && st->wave_jobs >= jobs && (!need_sum || (st->wave.sum && st->wave_sum_jobs >= sum_jobs))) return 0;
   if (st->d_wave) cudaFree(st->d_wave);  // cudaFree waits for queued work that still reads it
   st->d_wave = nullptr;
   st->wave_jobs = 0;
   const size_t n = (size_t)jobs;
   const size_t sz_ctl = 0, sz_hit = align256(n * sizeof(uint2)), sz_path = align256(n * sizeof(float4)),
-               sz_q = align256(n * 2 * sizeof(float4)), sz_sum = need_sum ? align256(n * sizeof(float4)) : 0;
+               sz_q = align256(n * 2 * sizeof(float4)), sz_sum = need_sum ? align256((size_t)sum_jobs * sizeof(float4)) : 0;
   const size_t total = sz_ctl + 2 * sz_hit + sz_path + 2 * sz_q + sz_sum;
   if (cudaMalloc(&st->d_wave, total) != cudaSuccess) {
     cudaGetLastError();
@@ -217,12 +219,13 @@ static int wave_reserve(RtState* st, uint64_t jobs, bool need_sum) {
   st->wave.q_bounce = reinterpret_cast<float4*>(p); p += sz_q;
   st->wave.sum = need_sum ? reinterpret_cast<float4*>(p) : nullptr;
   st->wave_jobs = jobs;
+  st->wave_sum_jobs = sum_jobs;
   return 0;
 }
 
 template <int STAGE, int SCHED, bool STATS>
 static int wave_trace(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, const WaveBufs& wb,
-                      cudaStream_t stream, uint32_t rows, uint32_t jobs, uint32_t s) {
+                      cudaStream_t stream, uint32_t rows, uint32_t jobs, uint32_t plane_jobs, uint32_t s_base) {
   const size_t smem = sizeof(uint2) * kSmStack * kWideThreads;
   int* occ = st->wave_blocks_per_sm + (STAGE * 6 + SCHED * 2 + (STATS ? 1 : 0));
   auto kernel = rt_wave_trace_kernel<STAGE, SCHED, STATS>;
@@ -239,73 +242,84 @@ static int wave_trace(vx_device* dev, RtState* st, const kernel_arg_t& a, const 
     const uint64_t need = ((uint64_t)jobs + kWideThreads - 1) / kWideThreads;
     if (need < grid) grid = need;
   }
-  kernel<<<(unsigned)grid, kWideThreads, smem, stream>>>(a, sc, wb, rows, jobs, s, st->d_counters);
+  kernel<<<(unsigned)grid, kWideThreads, smem, stream>>>(a, sc, wb, rows, jobs, plane_jobs, s_base, st->d_counters);
   return 0;
 }
 
-// One sample plane of one chain: the six launches of rt_wave.cuh for the jobs [wb.job_base, wb.job_base + jobs).
+// One chain of one pass: the five launches of rt_wave.cuh in front of the combine, for the jobs
+// [wb.job_base, wb.job_base + jobs) of the pass (job = pass-local sample * plane_jobs + pixel job).
 template <int SCHED, bool STATS>
 static int wave_chain(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, const WaveBufs& wb,
-                      cudaStream_t s, uint32_t rows, uint32_t jobs, uint32_t sample, uint32_t* launches) {
+                      cudaStream_t s, uint32_t rows, uint32_t jobs, uint32_t plane_jobs, uint32_t s_base,
+                      uint32_t* launches) {
   const float4* tris = sc.tris;
   const unsigned blocks = (jobs + 255u) / 256u;
   const unsigned sm_blocks = (unsigned)dev->prop.multiProcessorCount * 8u;
-  if (wave_trace<0, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, sample) != 0) return -1;
-  rt_wave_shade1_kernel<<<blocks, 256, 0, s>>>(a, tris, wb, rows, jobs, sample);
+  if (wave_trace<0, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
+  rt_wave_shade1_kernel<<<blocks, 256, 0, s>>>(a, tris, wb, rows, jobs, plane_jobs, s_base);
   *launches += 2;
   if (a.mode >= SRT_MODE_SHADOW) {
-    if (wave_trace<1, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, sample) != 0) return -1;
+    if (wave_trace<1, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
     *launches += 1;
   }
   if (a.mode >= SRT_MODE_BOUNCE) {
     rt_wave_shade2_kernel<<<blocks < sm_blocks ? blocks : sm_blocks, 256, 0, s>>>(a, tris, wb);
-    if (wave_trace<2, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, sample) != 0) return -1;
+    if (wave_trace<2, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
     *launches += 2;
   }
-  rt_wave_combine_kernel<<<blocks, 256, 0, s>>>(a, wb, rows, jobs, sample, st->d_counters);
-  *launches += 1;
   return 0;
 }
 
-// A frame = `chains` independent chains over disjoint job ranges (whole 256-job groups, so that the shading CTAs
-// of different chains never share a tile), each on its own stream.  Every trace kernel is persistent and ends with
-// a tail in which a few long rays keep a few warps busy (ncu: K5 of C3 ran at 30 % warps active); with two chains
-// the other chain's next kernel moves into the SM slots a tail frees, so the tails overlap useful work instead of
-// idling the GPU.  The chains share hit1 / path / sum (indexed by frame-wide job id) and split the queues; each
-// has its own control block.  Joined on the device stream before vx_start's closing event.
+// A frame = passes over sample ranges (one pass whenever pixels x samples fit the queue budget), each pass =
+// `chains` independent chains over disjoint job ranges (whole 256-job groups, so that the shading CTAs of different
+// chains never share a tile) on their own streams, joined in front of the combine.  Every trace kernel is persistent
+// and ends with a tail in which a few long rays keep a few warps busy (ncu: K5 of C3 ran at 30 % warps active);
+// with two chains the other chain's next kernel moves into the SM slots a tail frees, so the tails overlap useful
+// work instead of idling the GPU.  The chains share hit1 / path (indexed by pass-wide job id) and split the queues;
+// each has its own control block.
+constexpr uint64_t kWavePassJobs = 1ull << 27;  // 160 B of queues and path state per job: 21 GB at most
+
 template <int SCHED, bool STATS>
 static int wave_frame(vx_device* dev, RtState* st, const kernel_arg_t& a, const WideScene& sc, uint32_t rows,
-                      uint32_t jobs, uint32_t chains, uint32_t* launches) {
+                      uint32_t plane_jobs, uint32_t chains_wanted, uint32_t* launches) {
   cudaStream_t s0 = dev->stream;
-  const uint32_t groups = (jobs + 255u) / 256u;
-  if (chains > groups) chains = groups;
-  if (chains < 1u) chains = 1u;
+  const uint64_t budget = vx_dev_dcr(dev, VX_DCR_RT_PASS_JOBS) ? vx_dev_dcr(dev, VX_DCR_RT_PASS_JOBS) : kWavePassJobs;
+  uint32_t per_pass = (uint32_t)(budget / plane_jobs);  // samples per pass
+  if (per_pass < 1u) per_pass = 1u;
+  if (per_pass > a.spp) per_pass = a.spp;
+  if (wave_reserve(st, (uint64_t)plane_jobs * per_pass, per_pass < a.spp ? plane_jobs : 0) != 0) return -1;
   VX_CUDA_OK(cudaMemsetAsync(st->d_wave_ctl, 0, sizeof(WaveCtl) * kMaxChains, s0));
-  if (chains > 1u) {
-    VX_CUDA_OK(cudaEventRecord(st->chain_fork, s0));
-    for (uint32_t c = 1; c < chains; ++c) VX_CUDA_OK(cudaStreamWaitEvent(st->chain_stream[c - 1], st->chain_fork, 0));
-  }
-  WaveBufs wb[kMaxChains];
-  uint32_t n_jobs[kMaxChains];
-  for (uint32_t c = 0; c < chains; ++c) {
-    const uint32_t g0 = (uint32_t)((uint64_t)groups * c / chains), g1 = (uint32_t)((uint64_t)groups * (c + 1) / chains);
-    const uint32_t first = g0 * 256u, last = g1 * 256u < jobs ? g1 * 256u : jobs;
-    wb[c] = st->wave;
-    wb[c].job_base = first;
-    wb[c].ctl = st->d_wave_ctl + c;
-    wb[c].q_shadow = st->wave.q_shadow + 2 * (size_t)first;  // a chain queues at most one shadow / bounce ray per job
-    wb[c].q_bounce = st->wave.q_bounce + 2 * (size_t)first;
-    wb[c].hit2 = st->wave.hit2 + first;
-    n_jobs[c] = last - first;
-  }
-  for (uint32_t sample = 0; sample < a.spp; ++sample)
-    for (uint32_t c = 0; c < chains; ++c)
-      if (wave_chain<SCHED, STATS>(dev, st, a, sc, wb[c], c == 0 ? s0 : st->chain_stream[c - 1], rows, n_jobs[c], sample,
-                                   launches) != 0)
+  for (uint32_t s_first = 0; s_first < a.spp; s_first += per_pass) {
+    const uint32_t s_count = a.spp - s_first < per_pass ? a.spp - s_first : per_pass;
+    const uint32_t jobs = plane_jobs * s_count;
+    const uint32_t groups = (jobs + 255u) / 256u;
+    uint32_t chains = chains_wanted ? chains_wanted : (jobs >= (1u << 18) ? 2u : 1u);  // small passes are launch-bound
+    if (chains > (uint32_t)kMaxChains) chains = kMaxChains;
+    if (chains > groups) chains = groups;
+    if (chains > 1u) {
+      VX_CUDA_OK(cudaEventRecord(st->chain_fork, s0));
+      for (uint32_t c = 1; c < chains; ++c) VX_CUDA_OK(cudaStreamWaitEvent(st->chain_stream[c - 1], st->chain_fork, 0));
+    }
+    for (uint32_t c = 0; c < chains; ++c) {
+      const uint32_t g0 = (uint32_t)((uint64_t)groups * c / chains), g1 = (uint32_t)((uint64_t)groups * (c + 1) / chains);
+      const uint32_t first = g0 * 256u, last = g1 * 256u < jobs ? g1 * 256u : jobs;
+      WaveBufs wb = st->wave;
+      wb.job_base = first;
+      wb.ctl = st->d_wave_ctl + c;
+      wb.q_shadow = st->wave.q_shadow + 2 * (size_t)first;  // a chain queues at most one shadow / bounce ray per job
+      wb.q_bounce = st->wave.q_bounce + 2 * (size_t)first;
+      wb.hit2 = st->wave.hit2 + first;
+      if (wave_chain<SCHED, STATS>(dev, st, a, sc, wb, c == 0 ? s0 : st->chain_stream[c - 1], rows, last - first, plane_jobs,
+                                   s_first, launches) != 0)
         return -1;
-  for (uint32_t c = 1; c < chains; ++c) {
-    VX_CUDA_OK(cudaEventRecord(st->chain_join[c - 1], st->chain_stream[c - 1]));
-    VX_CUDA_OK(cudaStreamWaitEvent(s0, st->chain_join[c - 1], 0));
+    }
+    for (uint32_t c = 1; c < chains; ++c) {
+      VX_CUDA_OK(cudaEventRecord(st->chain_join[c - 1], st->chain_stream[c - 1]));
+      VX_CUDA_OK(cudaStreamWaitEvent(s0, st->chain_join[c - 1], 0));
+    }
+    rt_wave_combine_kernel<<<(plane_jobs + 255u) / 256u, 256, 0, s0>>>(a, st->wave, rows, plane_jobs, s_first, s_count,
+                                                                      st->d_wave_ctl, chains, st->d_counters);
+    *launches += 1;
   }
   return 0;
 }
@@ -490,12 +504,9 @@ int rt_launch(vx_device* dev, const kernel_arg_t& a) {
   if (wave) {
     const uint64_t jobs = (uint64_t)tiles * 32u;
     if (jobs > 0x7FFFFF00ull) return -1;
-    if (wave_reserve(st, jobs, a.spp > 1) != 0) return -1;
     uint32_t n = 0;
     int rc;
-    uint32_t chains = vx_dev_dcr(dev, VX_DCR_RT_CHAINS);
-    if (chains == 0u) chains = jobs >= (1u << 18) ? 2u : 1u;  // small frames are launch-bound: one chain
-    if (chains > (uint32_t)kMaxChains) chains = kMaxChains;
+    const uint32_t chains = vx_dev_dcr(dev, VX_DCR_RT_CHAINS);  // 0 = by pass size
     if (sched == SCHED_WHILE) rc = stats ? wave_frame<SCHED_WHILE, true>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n)
                                          : wave_frame<SCHED_WHILE, false>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n);
     else if (sched == SCHED_DEFER) rc = stats ? wave_frame<SCHED_DEFER, true>(dev, st, a, sc, rows, (uint32_t)jobs, chains, &n)

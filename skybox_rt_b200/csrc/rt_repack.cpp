@@ -2,19 +2,16 @@
 // reference's BVH builder output is repacked into a 16B-aligned SoA wide-BVH node and
 // precomputed-triangle layout").  Runs once per scene, on the first vx_start that sees it.
 //
-// Output layout (all 16-byte aligned, fetched with 128-bit read-only loads):
-//   Node8, 80 B = 5 x float4: an 8-wide node whose child boxes are stored as 8-bit offsets in a
-//   per-node frame (origin p, power-of-two scale per axis), children in SoA byte lanes
-//   (qlo_x[8] | qlo_y[8] | qlo_z[8] | qhi_x[8] | qhi_y[8] | qhi_z[8]).  Internal children are
-//   contiguous from child_base in slot order; the triangles of leaf children are contiguous from
-//   tri_base.  The format follows the published compressed wide BVH of Ylitie, Karras & Laine
-//   (HPG 2017); meta encoding and slot assignment are this repo's.
-//   Triangle records keep the builder's 48-byte (v0|prim, e1|albedo, e2|pad) form -- the operands
-//   of the intersection test must stay bit-identical -- and are only re-ordered.
+// Output layout: Node4 (rt_repack.h), 128 B = one cache line per 4-wide node, full-precision child boxes in SoA
+// planes, one child slot per TRIANGLE with the triangle's own box.  Triangle records keep the builder's 48-byte
+// (v0|prim, e1|albedo, e2|pad) form -- the operands of the intersection test must stay bit-identical -- and are
+// not even re-ordered: triangle refs index the app's record array.
+// (A compressed 8-wide node image after Ylitie, Karras & Laine was written in round 1 and never traversed; it was
+// removed in round 2 -- DESIGN.md section 7 has the measurements that decided against it.)
 //
-// Boxes are quantised OUTWARD after inflating them by delta = 2^-18 * max|root coordinate|, so a
-// decoded child box always contains the builder's box plus the slack the oracle's slab test uses
-// (DESIGN.md "Conservative box test").  Nothing here affects which triangle a ray reports.
+// Boxes are rounded OUTWARD after inflating them by delta = 2^-18 * max|root coordinate|, so a child box always
+// contains the builder's box plus the slack the oracle's slab test uses (DESIGN.md "Conservative box test").
+// Nothing here affects which triangle a ray reports.
 #include "rt_repack.h"
 
 #include <math.h>
@@ -25,71 +22,6 @@
 
 namespace srt {
 
-namespace {
-
-struct Child {
-  uint32_t node;  // BVH2 node index
-  float area;
-};
-
-inline float half_area(const srt_bvh2_node_t& n) {
-  const float dx = n.bmax[0] - n.bmin[0], dy = n.bmax[1] - n.bmin[1], dz = n.bmax[2] - n.bmin[2];
-  return dx * dy + dy * dz + dz * dx;
-}
-
-// children of wide node rooted at BVH2 node `root`: open the largest internal child until 8
-void collapse(const srt_bvh2_node_t* n2, uint32_t root, Child out[8], int& count) {
-  count = 0;
-  if (n2[root].count > 0) {  // a leaf root (tiny scene): one leaf child
-    out[count++] = Child{root, half_area(n2[root])};
-    return;
-  }
-  out[count++] = Child{n2[root].left_first, half_area(n2[n2[root].left_first])};
-  out[count++] = Child{n2[root].left_first + 1, half_area(n2[n2[root].left_first + 1])};
-  while (count < 8) {
-    int best = -1;
-    for (int i = 0; i < count; ++i)
-      if (n2[out[i].node].count == 0 && (best < 0 || out[i].area > out[best].area)) best = i;
-    if (best < 0) break;
-    const uint32_t l = n2[out[best].node].left_first;
-    out[best] = Child{l, half_area(n2[l])};
-    out[count++] = Child{l + 1, half_area(n2[l + 1])};
-  }
-}
-
-// slot = octant of the child centre relative to the node centre, so that visiting slots in the
-// order (slot ^ ray octant) approximates front-to-back.  Collisions take the nearest free slot.
-void assign_slots(const srt_bvh2_node_t* n2, const srt_bvh2_node_t& parent, const Child ch[8], int count,
-                  int slot_of[8]) {
-  bool used[8] = {false, false, false, false, false, false, false, false};
-  int want[8];
-  for (int i = 0; i < count; ++i) {
-    const srt_bvh2_node_t& c = n2[ch[i].node];
-    int s = 0;
-    for (int k = 0; k < 3; ++k) {
-      const float cc = c.bmin[k] + c.bmax[k], pc = parent.bmin[k] + parent.bmax[k];
-      if (cc > pc) s |= 1 << k;
-    }
-    want[i] = s;
-    slot_of[i] = -1;
-  }
-  for (int i = 0; i < count; ++i)
-    if (!used[want[i]]) { slot_of[i] = want[i]; used[want[i]] = true; }
-  for (int i = 0; i < count; ++i) {
-    if (slot_of[i] >= 0) continue;
-    int best = -1, bd = 99;
-    for (int s = 0; s < 8; ++s) {
-      if (used[s]) continue;
-      const int d = __builtin_popcount((unsigned)(s ^ want[i]));
-      if (d < bd) { bd = d; best = s; }
-    }
-    slot_of[i] = best;
-    used[best] = true;
-  }
-}
-
-}  // namespace
-
 float scene_delta_host(const srt_bvh2_node_t& root) {
   float m = 0.0f;
   for (int k = 0; k < 3; ++k) {
@@ -99,83 +31,15 @@ float scene_delta_host(const srt_bvh2_node_t& root) {
   return m * (1.0f / 262144.0f);
 }
 
-int repack_bvh8(const srt_bvh2_node_t* n2, uint32_t num_nodes, const srt_tri_rec_t* tris, uint32_t num_tris,
-                std::vector<Node8>& out_nodes, std::vector<srt_tri_rec_t>& out_tris) {
-  if (!n2 || !tris || num_nodes == 0 || num_tris == 0) return -1;
-  const double delta = (double)scene_delta_host(n2[0]);
-  out_nodes.clear();
-  out_tris.clear();
-  out_tris.reserve(num_tris);
-  out_nodes.reserve(num_nodes / 4 + 8);
-  std::vector<uint32_t> src;  // BVH2 node each wide node was built from (BFS order)
-  src.reserve(num_nodes / 4 + 8);
-  out_nodes.push_back(Node8());
-  src.push_back(0);
-  for (size_t w = 0; w < out_nodes.size(); ++w) {
-    const srt_bvh2_node_t& parent = n2[src[w]];
-    Child ch[8];
-    int count, slot_of[8];
-    collapse(n2, src[w], ch, count);
-    assign_slots(n2, parent, ch, count, slot_of);
-    int child_in_slot[8] = {-1, -1, -1, -1, -1, -1, -1, -1};
-    for (int i = 0; i < count; ++i) child_in_slot[slot_of[i]] = i;
-
-    Node8 nd;
-    memset(&nd, 0, sizeof(nd));
-    // frame: origin = inflated parent min (rounded down), scale = smallest 2^e covering the extent
-    int e[3];
-    double p[3];
-    for (int k = 0; k < 3; ++k) {
-      float pf = (float)((double)parent.bmin[k] - delta);
-      if ((double)pf > (double)parent.bmin[k] - delta) pf = nextafterf(pf, -INFINITY);
-      nd.p[k] = pf;
-      p[k] = (double)pf;
-      const double ext = ((double)parent.bmax[k] + delta) - p[k];
-      int ek = ext > 0.0 ? (int)ceil(log2(ext / 255.0)) : -100;
-      if (ek < -100) ek = -100;
-      while (ceil(ext / ldexp(1.0, ek)) > 255.0) ++ek;
-      if (ek > 100) return -1;  // coordinates beyond what the frame can represent
-      e[k] = ek;
-      nd.e[k] = (uint8_t)(ek + 127);
-    }
-    nd.child_base = (uint32_t)out_nodes.size();
-    nd.tri_base = (uint32_t)out_tris.size();
-    uint32_t rel = 0, tri_off = 0;
-    for (int s = 0; s < 8; ++s) {
-      const int i = child_in_slot[s];
-      if (i < 0) continue;  // meta 0 = empty slot; its boxes stay 0 and are never tested
-      const srt_bvh2_node_t& c = n2[ch[i].node];
-      for (int k = 0; k < 3; ++k) {
-        const double sc = ldexp(1.0, e[k]);
-        double lo = floor((((double)c.bmin[k] - delta) - p[k]) / sc);
-        double hi = ceil((((double)c.bmax[k] + delta) - p[k]) / sc);
-        lo = std::min(std::max(lo, 0.0), 255.0);
-        hi = std::min(std::max(hi, 0.0), 255.0);
-        nd.q[k][s] = (uint8_t)lo;
-        nd.q[3 + k][s] = (uint8_t)hi;
-      }
-      if (c.count > 0) {
-        if (c.count > 4 || tri_off + c.count > 32) return -1;
-        nd.meta[s] = (uint8_t)((c.count << 5) | tri_off);
-        for (uint32_t t = 0; t < c.count; ++t) out_tris.push_back(tris[c.left_first + t]);
-        tri_off += c.count;
-      } else {
-        nd.meta[s] = (uint8_t)((7u << 5) | rel);
-        nd.imask |= (uint8_t)(1u << s);
-        ++rel;
-        out_nodes.push_back(Node8());
-        src.push_back(ch[i].node);
-      }
-    }
-    out_nodes[w] = nd;
-  }
-  return out_tris.size() == num_tris ? 0 : -1;
-}
-
 // ------------------------------------------------------------------------------------------------
 // BVH2 -> Node4 (the layout the default traversal kernel reads, rt_wide.cuh)
 // ------------------------------------------------------------------------------------------------
 namespace {
+
+inline float half_area(const srt_bvh2_node_t& n) {
+  const float dx = n.bmax[0] - n.bmin[0], dy = n.bmax[1] - n.bmin[1], dz = n.bmax[2] - n.bmin[2];
+  return dx * dy + dy * dz + dz * dx;
+}
 
 inline float round_down(double v) {
   float f = (float)v;

@@ -15,9 +15,12 @@
 //   K6 combine one thread per job       -> radiance, sample sum, A8R8G8B8 pixel (coalesced in 8x4 tile order)
 //
 // The trace kernel does nothing but traverse: ~30 fewer registers than the megakernel, no path state machine,
-// and every shading instruction runs on full warps.  A multi-sample frame runs the six launches once per sample
-// index s = 0..spp-1; K6 adds sample s to a per-pixel sum, so the additions happen in sample order -- the
-// per-pixel loop's additions in its order, which keeps the frame bit-identical to the oracle's.
+// and every shading instruction runs on full warps.  A multi-sample frame runs as ONE pass over pixels x samples
+// jobs (job = sample * plane_jobs + pixel job, so 32 consecutive jobs are one sample of one 8x4 tile): six to
+// twelve launches per frame whatever spp is, and trace kernels whose queues are spp times longer (shorter tails).
+// K6 runs one thread per pixel and adds the pixel's samples in sample order -- the per-pixel loop's additions in
+// its order, which keeps the frame bit-identical to the oracle's.  Frames whose pixels x samples exceed the queue
+// budget run as several passes over sample ranges with a per-pixel running sum in between.
 //
 // All arithmetic that reaches a pixel is the shared no-FMA code of rt_device.cuh; which kernel evaluates it
 // (and with how many lanes) cannot change a bit.  Rays are appended to queues in arrival order, which varies from
@@ -47,7 +50,7 @@ struct WaveBufs {
   float4* q_shadow; // [jobs]  shadow rays of the stage in flight (K2 -> K3, then K4 -> K5)
   float4* q_bounce; // [2 * jobs] bounce rays (K2 -> K3, read again by K4)
   uint2* hit2;      // [jobs]  (t, record) per bounce-queue slot
-  float4* sum;      // [jobs]  running sample sum (spp > 1 only)
+  float4* sum;      // [plane_jobs]  running sample sum (only when a frame needs more than one pass)
 };
 constexpr float kBounceMissed = -1.0f;  // path.w of a path whose bounce ray left the scene (n.l values stored are >= 0)
 
@@ -87,7 +90,7 @@ __device__ __forceinline__ uint32_t queue_slot(uint32_t* counter, bool want) {
 template <int STAGE, int SCHED, bool STATS>
 __global__ void __launch_bounds__(kWideThreads, SRT_WAVE_MIN_BLOCKS)
 rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc, const WaveBufs wb, uint32_t rows,
-                     uint32_t cam_jobs, uint32_t s, unsigned long long* counters) {
+                     uint32_t cam_jobs, uint32_t plane_jobs, uint32_t s_base, unsigned long long* counters) {
   extern __shared__ uint2 s_stack[];
   uint2 spill[kLocalStack];
   Stack st;
@@ -127,11 +130,12 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
       my_job = job;
       if (STAGE == 0) {
         uint32_t x, ly;
-        my_job = job + wb.job_base;  // hit1 / path are indexed by the frame-wide job id
-        if (job_pixel(my_job, W, rows, tiles_x, x, ly)) {
+        my_job = job + wb.job_base;  // hit1 / path are indexed by the pass-wide job id = sample * plane_jobs + pixel job
+        const uint32_t sp = my_job / plane_jobs;
+        if (job_pixel(my_job - sp * plane_jobs, W, rows, tiles_x, x, ly)) {
           have_job = true;
           if (STATS) stats.rays += 1;
-          ray_setup(r, cam.eye, wave_camera_dir(a, cam, seed_hash, x, global_row(a, ly), s), 0.0f, false);
+          ray_setup(r, cam.eye, wave_camera_dir(a, cam, seed_hash, x, global_row(a, ly), s_base + sp), 0.0f, false);
           best.t = kTMax; best.prim = SRT_MISS; best.rec = SRT_MISS;
           st.reset();
           cu.go(0u);
@@ -160,11 +164,12 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
 // shadow ray's answer, so both go out together and K3 traces them in one launch.
 __global__ void __launch_bounds__(256)
 rt_wave_shade1_kernel(const __grid_constant__ kernel_arg_t a, const float4* __restrict__ tris, const WaveBufs wb,
-                      uint32_t rows, uint32_t cam_jobs, uint32_t s) {
+                      uint32_t rows, uint32_t cam_jobs, uint32_t plane_jobs, uint32_t s_base) {
   const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x, job = wb.job_base + local;
   const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
+  const uint32_t sp = job / plane_jobs, s = s_base + sp;
   uint32_t x = 0, ly = 0;
-  const bool live = local < cam_jobs && job_pixel(job, W, rows, tiles_x, x, ly);
+  const bool live = local < cam_jobs && job_pixel(job - sp * plane_jobs, W, rows, tiles_x, x, ly);
   bool want_shadow = false, want_bounce = false;
   float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0, b0 = s0, b1 = s0;
   if (live) {
@@ -253,47 +258,52 @@ rt_wave_shade2_kernel(const __grid_constant__ kernel_arg_t a, const float4* __re
   }
 }
 
-// ---- K6: combine, one thread per job: the radiance expression of the path, the sample sum, the pixel ------------
+// ---- K6: combine, one thread per PIXEL: the radiance expression of each of its samples, the sample sum, the pixel ----
 // Direct term k = ambient + n.l * visibility, written as the megakernel and the oracle branch it (visibility is
-// 0 or 1, an occluded or unlit hit has n.l stored as 0).  Also closes the plane: adds the queue sizes to the ray
-// counters and zeroes the control block for the next plane.
+// 0 or 1, an occluded or unlit hit has n.l stored as 0).  The pass holds samples [s_first, s_first + s_count) of
+// every pixel at job = (s - s_first) * plane_jobs + pixel job; they are added in sample order onto the running sum
+// of the earlier passes (wb.sum, only when s_first > 0) and the pixel is written when the last sample is in.
+// Also closes the pass: adds the queue sizes of all chains to the ray counters and zeroes their control blocks.
 __global__ void __launch_bounds__(256)
-rt_wave_combine_kernel(const __grid_constant__ kernel_arg_t a, const WaveBufs wb, uint32_t rows, uint32_t cam_jobs,
-                       uint32_t s, unsigned long long* counters) {
-  const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x, job = wb.job_base + local;
+rt_wave_combine_kernel(const __grid_constant__ kernel_arg_t a, const WaveBufs wb, uint32_t rows, uint32_t plane_jobs,
+                       uint32_t s_first, uint32_t s_count, WaveCtl* ctl, uint32_t chains, unsigned long long* counters) {
+  const uint32_t pj = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
   uint32_t x = 0, ly = 0;
-  if (local < cam_jobs && job_pixel(job, W, rows, tiles_x, x, ly)) {
-    V3 rad = ld3(a.sky);
-    const uint2 h = wb.hit1[job];
-    if (h.y != SRT_MISS) {
-      const float4 p = wb.path[job];
-      const V3 alb = unpack_albedo(__float_as_uint(p.x));
-      const float k1 = p.y > 0.0f ? a.ambient + p.y : a.ambient;
-      rad = alb * k1;
-      if (a.mode >= SRT_MODE_BOUNCE) {
-        V3 c2 = ld3(a.sky);
-        if (p.w != kBounceMissed) {
-          const float k2 = p.w > 0.0f ? a.ambient + p.w : a.ambient;
-          c2 = unpack_albedo(__float_as_uint(p.z)) * k2;
-        }
-        rad.x = rad.x + (alb.x * 0.5f) * c2.x;
-        rad.y = rad.y + (alb.y * 0.5f) * c2.y;
-        rad.z = rad.z + (alb.z * 0.5f) * c2.z;
-      }
-    }
+  if (pj < plane_jobs && job_pixel(pj, W, rows, tiles_x, x, ly)) {
     V3 sum = mk(0.0f, 0.0f, 0.0f);
-    if (s > 0) { const float4 q = wb.sum[job]; sum = mk(q.x, q.y, q.z); }
-    sum = sum + rad;
-    if (s + 1 < a.spp) {
-      wb.sum[job] = make_float4(sum.x, sum.y, sum.z, 0.0f);
+    if (s_first > 0) { const float4 q = wb.sum[pj]; sum = mk(q.x, q.y, q.z); }
+    for (uint32_t i = 0; i < s_count; ++i) {
+      const uint32_t job = i * plane_jobs + pj;
+      V3 rad = ld3(a.sky);
+      const uint2 h = wb.hit1[job];
+      if (h.y != SRT_MISS) {
+        const float4 p = wb.path[job];
+        const V3 alb = unpack_albedo(__float_as_uint(p.x));
+        const float k1 = p.y > 0.0f ? a.ambient + p.y : a.ambient;
+        rad = alb * k1;
+        if (a.mode >= SRT_MODE_BOUNCE) {
+          V3 c2 = ld3(a.sky);
+          if (p.w != kBounceMissed) {
+            const float k2 = p.w > 0.0f ? a.ambient + p.w : a.ambient;
+            c2 = unpack_albedo(__float_as_uint(p.z)) * k2;
+          }
+          rad.x = rad.x + (alb.x * 0.5f) * c2.x;
+          rad.y = rad.y + (alb.y * 0.5f) * c2.y;
+          rad.z = rad.z + (alb.z * 0.5f) * c2.z;
+        }
+      }
+      sum = sum + rad;
+    }
+    if (s_first + s_count < a.spp) {
+      wb.sum[pj] = make_float4(sum.x, sum.y, sum.z, 0.0f);
     } else {
       const V3 c = sum / (float)a.spp;
       *reinterpret_cast<uint32_t*>(a.cbuf_addr + (uint64_t)x * a.cbuf_stride + (uint64_t)ly * a.cbuf_pitch) = pack_argb(c);
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    WaveCtl* c = wb.ctl;
+  if (blockIdx.x == 0 && threadIdx.x < chains) {
+    WaveCtl* c = ctl + threadIdx.x;
     atomicAdd(counters + CTR_RAYS_SHADOW, (unsigned long long)c->n_shadow1 + c->n_shadow2);
     atomicAdd(counters + CTR_RAYS_BOUNCE, (unsigned long long)c->n_bounce);
     c->n_shadow1 = c->n_bounce = c->n_shadow2 = 0u;

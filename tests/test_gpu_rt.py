@@ -79,6 +79,27 @@ def test_wavefront_chains_do_not_change_the_frame(terrain, chains, w, h, mode, s
     assert ray_counts(c) == ray_counts(ctr)
 
 
+@pytest.mark.parametrize("pass_jobs", [1, 45000, 70000])  # 1 / 2 / 3 samples per pass of the 20 800-job plane
+@pytest.mark.parametrize("chains", [1, 2])
+def test_wavefront_sample_passes_keep_the_sample_order(terrain, pass_jobs, chains):
+    """A frame whose pixels x samples exceed the queue budget runs as several passes with a running per-pixel sum;
+    the additions must stay in sample order (bit-identical frame).  VX_DCR_RT_PASS_JOBS shrinks the budget."""
+    tracer, (onodes, otris), _ = terrain
+    dev = tracer.dev
+    dev.dcr_write(vx.VX_DCR_RT_VARIANT, vx.RT_VARIANT_WAVE)
+    dev.dcr_write(vx.VX_DCR_RT_CHAINS, chains)
+    dev.dcr_write(vx.VX_DCR_RT_PASS_JOBS, pass_jobs)
+    try:
+        fb = tracer.render(rt.make_arg(201, 97, 2, spp=5, seed=41, scene="terrain"))
+        c = tracer.counters()
+    finally:
+        dev.dcr_write(vx.VX_DCR_RT_CHAINS, 0)
+        dev.dcr_write(vx.VX_DCR_RT_PASS_JOBS, 0)
+    ref, ctr = o.render(o.make_arg(201, 97, 2, spp=5, seed=41, scene="terrain"), onodes, otris)
+    assert np.array_equal(fb, ref), f"{(fb != ref).sum()} of {fb.size} pixels differ"
+    assert ray_counts(c) == ray_counts(ctr)
+
+
 @pytest.mark.parametrize("variant", VARIANTS)
 def test_explicit_rays_hit_records_bit_exact(terrain, variant):
     tracer, (onodes, otris), soup = terrain
