@@ -286,7 +286,7 @@ void srt_draw3d_close(srt_draw3d_t* r) { /* cleanup(), main.cpp:137-146 (the dev
 
 int srt_draw3d_clear(srt_draw3d_t* r) { /* main.cpp:478-490 */
   int rc;
-  if (r->flags & SRT_DRAW3D_DEVICE_CLEAR) {
+  if ((r->flags & SRT_DRAW3D_DEVICE_CLEAR) || ((r->flags & SRT_DRAW3D_AUTO) && (uint64_t)r->width * r->height >= (1u << 20))) {
     rc = vx_cuda_fill32(r->depth_buffer, 0, r->zbuf_size, 0xffffffffu);
     if (rc == 0) rc = vx_cuda_fill32(r->color_buffer, 0, r->cbuf_size, 0xff000000u);
     r->stats.h2d_bytes = 0;
@@ -310,7 +310,7 @@ static int stage_draw(srt_draw3d_t* r, const srt_trace_t* trace, const srt_drawc
   double t0 = now_ms(), t1;
   int rc;
   *tex_out = NULL;
-  if (r->flags & SRT_DRAW3D_GPU_BINNING) {
+  if ((r->flags & SRT_DRAW3D_GPU_BINNING) || ((r->flags & SRT_DRAW3D_AUTO) && dc->num_primitives >= 10000u)) {
     /* the pre-pass on the device: upload the draw's vertices and indices instead of its binned form */
     vx_buffer_h vb = NULL, ib = NULL;
     srt_binning_info_t info;
@@ -398,7 +398,7 @@ int srt_draw3d_render(srt_draw3d_t* r, const srt_trace_t* trace, uint32_t start_
     CHECK(vx_upload_bytes(r->device, &r->kernel_arg, sizeof(r->kernel_arg), &r->args_buffer));
     r->stats.h2d_bytes += sizeof(r->kernel_arg);
     CHECK(vx_start(r->device, r->krnl_buffer, r->args_buffer));
-    CHECK(vx_ready_wait(r->device, VX_MAX_TIMEOUT));
+    if (!(r->flags & SRT_DRAW3D_AUTO)) CHECK(vx_ready_wait(r->device, VX_MAX_TIMEOUT)); /* main.cpp:357 */
     r->stats.run_ms += now_ms() - t0;
   }
   return 0;
@@ -453,6 +453,14 @@ int srt_draw3d_read(srt_draw3d_t* r, uint32_t* cbuf, uint32_t* zbuf) { /* main.c
   if (zbuf) { CHECK(vx_copy_from_dev(zbuf, r->depth_buffer, 0, r->zbuf_size)); r->stats.d2h_bytes += r->zbuf_size; }
   return 0;
 }
+
+int srt_draw3d_read_async(srt_draw3d_t* r, uint32_t* cbuf, uint64_t* ticket) {
+  CHECK(vx_cuda_copy_from_dev_async(cbuf, r->color_buffer, 0, r->cbuf_size, ticket));
+  r->stats.d2h_bytes = r->cbuf_size;
+  return 0;
+}
+
+int srt_draw3d_read_wait(srt_draw3d_t* r, uint64_t ticket) { return vx_cuda_copy_wait(r->device, ticket); }
 
 const srt_draw3d_stats_t* srt_draw3d_stats(const srt_draw3d_t* r) { return &r->stats; }
 vx_buffer_h srt_draw3d_color_buffer(const srt_draw3d_t* r) { return r->color_buffer; }

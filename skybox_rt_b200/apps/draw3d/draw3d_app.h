@@ -34,6 +34,11 @@ extern "C" {
 #define SRT_DRAW3D_GPU_BINNING 0x10 /* triangle setup + binning on the device (vx_cuda_draw3d_binning): vertices and
                                        indices are uploaded instead of primbuf / tilebuf; same bytes, same frame */
 
+#define SRT_DRAW3D_AUTO 0x40 /* pick per frame / per draw what is faster on this back-end, same pixels: device-side clear for
+                                targets of >= 2^20 pixels, device binning for draws of >= 10^4 triangles, and no
+                                vx_ready_wait between the draws of a frame (they queue on the device in order; buffers of
+                                a finished draw are freed stream-ordered).  Without it the loop is the reference's.       */
+
 typedef struct srt_draw3d srt_draw3d_t;
 
 typedef struct {
@@ -76,6 +81,12 @@ int srt_draw3d_submit(srt_draw3d_t* r);
 
 /* Colour (and optionally depth) buffer read-back; width*height u32 each, row 0 = framebuffer row 0. */
 int srt_draw3d_read(srt_draw3d_t* r, uint32_t* cbuf, uint32_t* zbuf);
+
+/* Colour read-back that returns at once (vx_cuda_copy_from_dev_async): ordered after the draws queued so far, it runs
+ * while the next frame renders into ANOTHER srt_draw3d_t; cbuf should be page-locked.  srt_draw3d_read_wait blocks
+ * until the ticket's bytes are on the host.  This app object must not be cleared or drawn to before that. */
+int srt_draw3d_read_async(srt_draw3d_t* r, uint32_t* cbuf, uint64_t* ticket);
+int srt_draw3d_read_wait(srt_draw3d_t* r, uint64_t ticket);
 
 const srt_draw3d_stats_t* srt_draw3d_stats(const srt_draw3d_t* r);
 vx_buffer_h srt_draw3d_color_buffer(const srt_draw3d_t* r);

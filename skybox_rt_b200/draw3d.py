@@ -18,6 +18,7 @@ APP_LIB = os.path.join(PKG, "lib", "libdraw3d_app.so")
 HOST_LIB = os.path.join(PKG, "lib", "libskybox_rt_host.so")
 
 SW_RAST, SW_OM, SW_TEX, WIDE_TILES, GPU_BINNING, DEVICE_CLEAR = 1, 2, 4, 8, 16, 32
+AUTO = 64  # device clear / device binning where they pay, no wait between the draws of a frame (draw3d_app.h)
 TILEBUF_REFERENCE, TILEBUF_WIDE = 0, 1
 VX_CSR_RASTER_FRAGMENTS, VX_CSR_RASTER_QUAD_TESTS, VX_CSR_RASTER_TILES = 0x7C8, 0x7C9, 0x7CA
 VX_DCR_RASTER_EXT_TBUF_FORMAT = 0x804
@@ -93,6 +94,8 @@ def app_lib():
         L.srt_draw3d_prepare.argtypes = [vp, C.POINTER(TraceStruct)]
         L.srt_draw3d_submit.argtypes = [vp]
         L.srt_draw3d_read.argtypes = [vp, vp, vp]
+        L.srt_draw3d_read_async.argtypes = [vp, vp, C.POINTER(C.c_uint64)]
+        L.srt_draw3d_read_wait.argtypes = [vp, C.c_uint64]
         L.srt_draw3d_stats.argtypes = [vp]
         L.srt_draw3d_stats.restype = C.POINTER(Stats)
         L.srt_draw3d_color_buffer.argtypes = [vp]
@@ -256,6 +259,16 @@ class Draw3D:
         cp = c.data_ptr() if hasattr(c, "data_ptr") else c.ctypes.data
         self._ck(app_lib().srt_draw3d_read(self.h, cp, z.ctypes.data if depth else None), "srt_draw3d_read")
         return (c, z) if depth else c
+
+    def read_async(self, out):
+        """Colour read-back that overlaps the next frame (rendered by another Draw3D): returns a ticket."""
+        t = C.c_uint64()
+        cp = out.data_ptr() if hasattr(out, "data_ptr") else out.ctypes.data
+        self._ck(app_lib().srt_draw3d_read_async(self.h, cp, C.byref(t)), "srt_draw3d_read_async")
+        return t.value
+
+    def read_wait(self, ticket):
+        self._ck(app_lib().srt_draw3d_read_wait(self.h, ticket), "srt_draw3d_read_wait")
 
     def buffer_addresses(self):
         """(colour, depth) device addresses as vx_mem_address reports them (CUDA device pointers)."""

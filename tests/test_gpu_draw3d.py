@@ -65,6 +65,39 @@ def test_hardware_unit_path_equals_software_path(d3, name):
     assert np.array_equal(hw[0], sw[0]) and np.array_equal(hw[1], sw[1])
 
 
+@pytest.mark.parametrize("name", ["vase", "polybump", "tekkaman"])
+@pytest.mark.parametrize("w,h", [(1280, 1024), (300, 200)])  # above / below the device-clear threshold of 2^20 pixels
+def test_auto_flow_and_async_read_back_equal_the_reference_flow(d3, name, w, h):
+    """SRT_DRAW3D_AUTO (device clear, device binning for large draws, no wait between draws) and the asynchronous
+    read-back change how the frame gets made and fetched, not one word of it: two app objects alternate frames the
+    way the pipelined e2e loop of bench_draw3d.py does."""
+    import torch
+    from skybox_rt_b200 import vortex as vx
+    t = d3.Trace(blob=od.trace_blob(name))
+    with vx.Device() as dev:
+        ref_app = d3.Draw3D(w, h, flags=ALL_SW | d3.WIDE_TILES, device=dev)
+        ref, zref = ref_app.frame(t, depth=True)
+        ref_app.close()
+        apps = [d3.Draw3D(w, h, flags=ALL_SW | d3.WIDE_TILES | d3.AUTO, device=dev) for _ in range(2)]
+        host = [torch.empty(h * w, dtype=torch.int32).pin_memory() for _ in range(2)]
+        tickets = [None, None]
+        for i in range(4):
+            a = apps[i & 1]
+            if tickets[i & 1] is not None:
+                a.read_wait(tickets[i & 1])
+                assert np.array_equal(host[i & 1].numpy().view(np.uint32).reshape(h, w), ref)
+            a.clear()
+            a.render(t)
+            tickets[i & 1] = a.read_async(host[i & 1])
+        for j in (0, 1):
+            apps[j].read_wait(tickets[j])
+            assert np.array_equal(host[j].numpy().view(np.uint32).reshape(h, w), ref)
+        _, z = apps[1].read(depth=True)
+        assert np.array_equal(z, zref)
+        for a in apps:
+            a.close()
+
+
 @pytest.mark.parametrize("name", ["evilskull", "polybump"])
 def test_prepared_resubmission_equals_per_draw_render(d3, name):
     t = d3.Trace(blob=od.trace_blob(name))
