@@ -153,13 +153,15 @@ def native_arm(args, ClockSampler, load_peaks):
     draws = prep["draws_submitted"]
 
     if world > 1:
-        from skybox_rt_b200.formats import rank_row_index
-        from skybox_rt_b200.multi import FrameGather
-        fg = FrameGather(W, H, TILE, torch.device("cuda", local))
-        my_rows = torch.as_tensor(rank_row_index(H, TILE, world, rank), device="cuda")
+        # one NCCL exchange per frame through the C entry vx_cuda_frame_gather_inplace: every rank renders its tile rows
+        # at their final positions of a full-size colour buffer, the root receives the other ranks' 32-row blocks
+        # straight into its own buffer; torch.distributed only carries the communicator id
+        ident = [vx.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ident, src=0)
+        comm = vx.Comm(dev, ident[0], rank, world)
 
-        def gather():
-            return fg.gather(cbuf.index_select(0, my_rows))
+        def gather(a=None):
+            comm.frame_gather_inplace((a or app).color_buffer_handle(), W, H, TILE, 0)
     else:
         gather = None
 
@@ -248,11 +250,11 @@ def native_arm(args, ClockSampler, load_peaks):
         app2.clear()
         app2.render(trace)
         if gather:
-            with torch.cuda.stream(stream):
-                frame = fg.gather(cbuf2.index_select(0, my_rows))
-                if rank == 0:
-                    host_frame.copy_(frame.view(-1), non_blocking=True)
-            stream.synchronize()
+            gather(app2)  # queued behind the draws; rank 0's colour buffer then holds the whole frame
+            if rank == 0:
+                app2.read(out=host_frame)
+            else:
+                dev.ready_wait()
         else:
             app2.read(out=host_frame)
     e2e_step()

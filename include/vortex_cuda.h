@@ -129,6 +129,12 @@ int vx_cuda_comm_destroy(vx_comm_h hcomm);
 int vx_cuda_frame_gather(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h strip, vx_buffer_h frame, uint32_t width,
                          uint32_t height, uint32_t rows_per_block, uint32_t root);
 
+/* The same exchange for ranks that render into FULL-SIZE frame buffers with their row blocks at the final positions
+ * (the raster path deals 32-row tile rows round-robin): the root receives every other rank's blocks straight into
+ * its own `frame` at the same offsets; no staging, no de-interleave.  Every rank passes its full-size buffer. */
+int vx_cuda_frame_gather_inplace(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h frame, uint32_t width, uint32_t height,
+                                 uint32_t rows_per_block, uint32_t root);
+
 /* Concatenating gather for record lists split over the ranks (hit records of a ray list): rank r's `bytes` bytes of
  * `src` land at offsets[r] of the root's `dst`; offsets / sizes (num_ranks entries each, sizes[r] == that rank's
  * `bytes`) are read on the root only.  Same ordering rules as vx_cuda_frame_gather. */

@@ -104,8 +104,6 @@ __device__ __forceinline__ F8 ldg256(const float4* p) {
                : "l"(p));
   return r;
 }
-constexpr uint32_t kTriBitRef = 0x80000000u;
-__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ float4 sel4(bool c, const float4 a, const float4 b) {
   return make_float4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w);
 }
@@ -207,14 +205,6 @@ __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const
   next = e1 ? c1 : next;
   next = e0 ? c0 : next;
   const bool p0 = h0 && !e0, p1 = h1 && !e1, p2 = h2 && !e2, p3 = h3 && (e0 || e1 || e2);
-#ifdef SRT_PREFETCH_PUSHED
-  // HBM-resident scenes: a pushed child is visited later with good probability and costs a DRAM round trip then;
-  // ask the L2 for its line now (one line per Node4; the first 32-byte sector of a triangle record)
-  if (p0) prefetch_l2(c0 & kTriBitRef ? (const void*)(sc.tris + 3u * (size_t)(c0 & 0x7FFFFFFFu)) : (const void*)(sc.nodes + 8u * (size_t)c0));
-  if (p1) prefetch_l2(c1 & kTriBitRef ? (const void*)(sc.tris + 3u * (size_t)(c1 & 0x7FFFFFFFu)) : (const void*)(sc.nodes + 8u * (size_t)c1));
-  if (p2) prefetch_l2(c2 & kTriBitRef ? (const void*)(sc.tris + 3u * (size_t)(c2 & 0x7FFFFFFFu)) : (const void*)(sc.nodes + 8u * (size_t)c2));
-  if (p3) prefetch_l2(c3 & kTriBitRef ? (const void*)(sc.tris + 3u * (size_t)(c3 & 0x7FFFFFFFu)) : (const void*)(sc.nodes + 8u * (size_t)c3));
-#endif
   if (st.top - st.base <= kSmStackBytes - 3u * kStackStride) {  // common case: predicated stores, no branches
     if (p3) { sts64(st.top, c3, __float_as_uint(t3)); st.top += kStackStride; }
     if (p2) { sts64(st.top, c2, __float_as_uint(t2)); st.top += kStackStride; }

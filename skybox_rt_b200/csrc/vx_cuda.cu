@@ -106,6 +106,8 @@ int vx_dev_open(vx_device_h* hdevice) {
   dev->raster = nullptr;
   dev->copy_stream = nullptr;
   dev->copy_next_ticket = 0;
+  dev->stage_ring = nullptr;
+  dev->stage_next = 0;
   dev->last_raster_tiles = 0;
   dev->last_raster_fragments = dev->last_raster_tests = 0;
   dev->run_recorded = false;
@@ -151,6 +153,11 @@ int vx_dev_close(vx_device_h hdevice) {
     for (cudaEvent_t e : dev->copy_done) cudaEventDestroy(e);
     cudaStreamDestroy(dev->copy_stream);
     dev->copy_stream = nullptr;
+  }
+  if (dev->stage_ring) {
+    for (cudaEvent_t e : dev->stage_done) cudaEventDestroy(e);
+    cudaFreeHost(dev->stage_ring);
+    dev->stage_ring = nullptr;
   }
   if (env_int("VORTEX_PROFILING", 0) != 0) vx_dump_perf(hdevice, stdout);  // stub/vortex.cpp:99-104
   srt::rt_destroy(dev);
@@ -240,6 +247,11 @@ int vx_mem_info(vx_device_h hdevice, uint64_t* mem_free, uint64_t* mem_used) {
   return 0;
 }
 
+static bool staged_uploads_enabled() {  // VX_CUDA_STAGED_UPLOADS=0: every upload blocks on the stream (A/B)
+  static const bool on = env_int("VX_CUDA_STAGED_UPLOADS", 1) != 0;
+  return on;
+}
+
 int vx_copy_to_dev(vx_buffer_h hbuffer, const void* host_ptr, uint64_t dst_offset, uint64_t size) {
   if (nullptr == hbuffer || nullptr == host_ptr) return -1;
   vx_buffer* b = as_buf(hbuffer);
@@ -253,6 +265,25 @@ int vx_copy_to_dev(vx_buffer_h hbuffer, const void* host_ptr, uint64_t dst_offse
     // loop that uploads a new kernel_arg_t per frame keeps the device busy.
     memcpy(b->shadow + dst_offset, host_ptr, size);
     VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, b->shadow + dst_offset, size, cudaMemcpyHostToDevice, dev->stream));
+  } else if (size <= kStageSlotBytes && staged_uploads_enabled()) {
+    // Medium uploads (a draw's tile / primitive buffers, textures): the bytes are copied into a slot of a page-locked
+    // ring and travel from there, queued on the launch stream behind the kernels already in it.  The caller's buffer
+    // is free on return, as the reference's blocking copy promises (runtime/simx/vortex.cpp:138-153), but the host
+    // does not wait for the device: it goes on binning the next draw while this one renders.  A slot is reused
+    // only after the transfer that read it last has completed.
+    if (!dev->stage_ring) {
+      VX_CUDA_OK(cudaHostAlloc(&dev->stage_ring, kStageSlots * kStageSlotBytes, cudaHostAllocDefault));
+      for (cudaEvent_t& e : dev->stage_done) VX_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      dev->stage_next = 0;
+    }
+    const uint32_t slot = dev->stage_next % kStageSlots;
+    if (dev->stage_next >= (uint32_t)kStageSlots) VX_CUDA_OK(cudaEventSynchronize(dev->stage_done[slot]));
+    uint8_t* stage = dev->stage_ring + (uint64_t)slot * kStageSlotBytes;
+    memcpy(stage, host_ptr, size);
+    VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, stage, size, cudaMemcpyHostToDevice, dev->stream));
+    VX_CUDA_OK(cudaEventRecord(dev->stage_done[slot], dev->stream));
+    dev->stage_next++;
+    if (dev->stage_next >= 2u * kStageSlots) dev->stage_next -= kStageSlots;  // keep ">= kStageSlots" true, no overflow
   } else {
     VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, host_ptr, size, cudaMemcpyHostToDevice, dev->stream));
     VX_CUDA_OK(cudaStreamSynchronize(dev->stream));

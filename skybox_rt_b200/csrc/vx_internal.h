@@ -32,6 +32,8 @@ struct vx_buffer {
 };
 
 constexpr uint64_t kShadowMaxBytes = 4096;
+constexpr int kStageSlots = 8;
+constexpr uint64_t kStageSlotBytes = 4ull << 20;
 
 // Device-side counters written by the kernels (one u64 each).
 enum {
@@ -65,6 +67,11 @@ struct vx_device {
   cudaEvent_t copy_fork;        // launch stream -> copy stream ordering
   cudaEvent_t copy_done[16];
   uint64_t copy_next_ticket;
+  // staged uploads (vx_copy_to_dev of up to kStageSlotBytes): page-locked ring the caller's bytes are copied into, so
+  // that the transfer is queued on the launch stream and the host does not wait for the kernels in front of it
+  uint8_t* stage_ring;          // kStageSlots x kStageSlotBytes, cudaHostAlloc'ed at the first staged upload
+  cudaEvent_t stage_done[8];
+  uint32_t stage_next;
   bool run_recorded;            // ev_start/ev_stop bracket the last vx_start
   std::map<uint32_t, uint32_t> dcrs;
   vx_buffer* buffers;           // intrusive list of live allocations

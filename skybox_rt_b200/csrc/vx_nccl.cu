@@ -211,6 +211,40 @@ int vx_cuda_frame_gather(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h hstri
   return 0;
 }
 
+// Frames whose ranks render into FULL-SIZE buffers at the rows' final positions (the raster path: tile rows dealt
+// round-robin, every rank's colour buffer has the frame's geometry): the root receives every other rank's row blocks
+// straight into its own buffer at the same offsets -- no staging copy, no de-interleave pass; (N-1)/N of the frame
+// crosses NVLink once.  One NCCL group of ceil(height / rows_per_block) * (N-1)/N receives.
+int vx_cuda_frame_gather_inplace(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h hframe, uint32_t width, uint32_t height,
+                                 uint32_t rows_per_block, uint32_t root) {
+  if (nullptr == hdevice || nullptr == hcomm || nullptr == hframe || width == 0 || height == 0 || rows_per_block == 0) return -1;
+  vx_device* dev = static_cast<vx_device*>(hdevice);
+  vx_comm* c = static_cast<vx_comm*>(hcomm);
+  if (c->dev != dev || root >= c->num_ranks) return -1;
+  vx_buffer* frame = static_cast<vx_buffer*>(hframe);
+  const uint64_t row_bytes = (uint64_t)width * 4u;
+  if (frame->size < (uint64_t)height * row_bytes) return -1;
+  if (c->num_ranks == 1) return 0;
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  const uint32_t blocks = (height + rows_per_block - 1) / rows_per_block;
+  VX_NCCL_OK(g_nccl.GroupStart());
+  for (uint32_t b = 0; b < blocks; ++b) {
+    const uint32_t owner = b % c->num_ranks;
+    if (owner == root || (c->rank != root && c->rank != owner)) continue;
+    const uint32_t y0 = b * rows_per_block, rows = height - y0 < rows_per_block ? height - y0 : rows_per_block;
+    char* p = static_cast<char*>(frame->dptr) + (uint64_t)y0 * row_bytes;
+    ncclResult_t r = c->rank == root ? g_nccl.Recv(p, (uint64_t)rows * row_bytes, ncclUint8, (int)owner, c->comm, dev->stream)
+                                     : g_nccl.Send(p, (uint64_t)rows * row_bytes, ncclUint8, (int)root, c->comm, dev->stream);
+    if (r != ncclSuccess) {
+      g_nccl.GroupEnd();
+      fprintf(stderr, "[VXDRV] NCCL error in vx_cuda_frame_gather_inplace: %s\n", g_nccl.GetErrorString(r));
+      return -1;
+    }
+  }
+  VX_NCCL_OK(g_nccl.GroupEnd());
+  return 0;
+}
+
 int vx_cuda_gather_bytes(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h hsrc, uint64_t bytes, vx_buffer_h hdst,
                          const uint64_t* offsets, const uint64_t* sizes, uint32_t root) {
   if (nullptr == hdevice || nullptr == hcomm) return -1;

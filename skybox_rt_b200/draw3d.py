@@ -270,6 +270,10 @@ class Draw3D:
     def read_wait(self, ticket):
         self._ck(app_lib().srt_draw3d_read_wait(self.h, ticket), "srt_draw3d_read_wait")
 
+    def color_buffer_handle(self):
+        """vx_buffer_h of the colour target (for vx_cuda_frame_gather_inplace / vx_cuda_copy_from_dev_async)."""
+        return C.c_void_p(app_lib().srt_draw3d_color_buffer(self.h))
+
     def buffer_addresses(self):
         """(colour, depth) device addresses as vx_mem_address reports them (CUDA device pointers)."""
         out = []

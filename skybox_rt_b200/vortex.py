@@ -53,7 +53,7 @@ CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx
                 "vx_cuda_perf_totals", "vx_cuda_draw3d_binning", "vx_cuda_rt_build_lbvh",
                 "vx_cuda_rt_node4_image", "vx_cuda_fill32", "vx_cuda_probe_read_bandwidth",
                 "vx_cuda_comm_unique_id", "vx_cuda_comm_init", "vx_cuda_comm_destroy", "vx_cuda_frame_gather",
-                "vx_cuda_gather_bytes", "vx_cuda_copy_from_dev_async", "vx_cuda_copy_wait"]  # include/vortex_cuda.h
+                "vx_cuda_gather_bytes", "vx_cuda_frame_gather_inplace", "vx_cuda_copy_from_dev_async", "vx_cuda_copy_wait"]  # include/vortex_cuda.h
 VX_CUDA_COMM_ID_BYTES = 128
 
 _lib = None
@@ -99,6 +99,7 @@ def lib():
             "vx_cuda_comm_unique_id": [vp], "vx_cuda_comm_init": [vp, vp, u32, u32, C.POINTER(vp)],
             "vx_cuda_comm_destroy": [vp], "vx_cuda_frame_gather": [vp, vp, vp, vp, u32, u32, u32, u32],
             "vx_cuda_gather_bytes": [vp, vp, vp, u64, vp, C.POINTER(u64), C.POINTER(u64), u32],
+            "vx_cuda_frame_gather_inplace": [vp, vp, vp, u32, u32, u32, u32],
             "vx_cuda_draw3d_binning": [vp, vp, u32, vp, u32, C.c_float, C.c_float, u32, u32, u32, u32, u32, u32,
                                        C.POINTER(vp), C.POINTER(vp), vp],
         }
@@ -191,6 +192,12 @@ class Comm:
         """Asynchronous on the launch stream: strips -> the root's `frame` buffer (None on the other ranks)."""
         _check(lib().vx_cuda_frame_gather(self.dev.handle, self.handle, strip.handle, frame.handle if frame else None,
                                           width, height, rows_per_block, root), "vx_cuda_frame_gather")
+
+    def frame_gather_inplace(self, frame_handle, width, height, rows_per_block, root=0):
+        """Row blocks of full-size per-rank frame buffers -> the root's buffer, in place (vx_cuda_frame_gather_inplace);
+        frame_handle: a vx_buffer_h (e.g. srt_draw3d_color_buffer)."""
+        _check(lib().vx_cuda_frame_gather_inplace(self.dev.handle, self.handle, frame_handle, width, height, rows_per_block,
+                                                  root), "vx_cuda_frame_gather_inplace")
 
     def gather_bytes(self, src, nbytes, dst=None, offsets=None, sizes=None, root=0):
         n = self.num_ranks

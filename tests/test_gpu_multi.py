@@ -98,3 +98,18 @@ def test_c_app_two_ranks_equal_single_gpu_png(native, tmp_path, size, mode, spp)
     r2 = subprocess.run([exe] + common + ["-g", "2", "-o", two, "-r", one], capture_output=True, text=True, timeout=180, env=env)
     assert r2.returncode == 0, r2.stdout + r2.stderr
     assert "PASSED!" in r2.stdout and "rank 0 of 2 joined" in r2.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(_gpus() < 2, reason="needs two GPUs (gpurun --gpus 2)")
+@pytest.mark.parametrize("kind", ["rt", "raster"])
+def test_two_ranks_gathered_through_the_c_abi_equal_the_single_gpu_frame(native, kind):
+    """tests/_multi_driver.py under torch.distributed.run: vx_cuda_frame_gather (RT strips) and
+    vx_cuda_frame_gather_inplace (raster tile rows) against the frame rank 0 renders alone."""
+    import sys
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29641" if kind == "rt" else "29642",
+                        os.path.join(ROOT, "tests", "_multi_driver.py"), kind], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "0 words differ" in r.stdout
