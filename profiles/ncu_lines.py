@@ -1,7 +1,7 @@
 """Per-source-line view of an .ncu-rep captured with --import-source on (kernels built with -lineinfo):
 share of warp instructions, average active threads per instruction and stall samples per CUDA line, for ONE kernel
 (the source page of a multi-kernel report lists every kernel; -k picks which).
-usage: python profiles/ncu_lines.py gpurun_out/x.ncu-rep [top_n] [-k kernel-regex] [--budget rays] > profiles/x_lines.txt
+usage: python profiles/ncu_lines.py gpurun_out/x.ncu-rep [top_n] [-k kernel-regex] [--skip n] [--budget rays] > profiles/x_lines.txt
 --budget N: also print the thread-instruction budget per ray by phase (node step / triangle test / scheduler /
             advance + job fetch / other), N = rays the captured launch traced."""
 import csv
@@ -56,10 +56,12 @@ def function_ranges(src):
     return out
 
 
-def main(path, top=40, kernel=None, rays=None):
+def main(path, top=40, kernel=None, rays=None, skip=0):
     cmd = ["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "cuda,sass"]
     if kernel:
-        cmd += ["-k", "regex:" + kernel]
+        cmd += ["-k", "regex:" + kernel]  # matches the function name without template arguments
+    if skip or kernel:
+        cmd += ["-s", str(skip), "-c", "1"]  # the skip-th matching launch of the report
     raw = subprocess.run(cmd, capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     fname, fpath, head, lines, kname = None, None, None, {}, None
@@ -131,5 +133,6 @@ if __name__ == "__main__":
     a = sys.argv[1:]
     kern = a[a.index("-k") + 1] if "-k" in a else None
     rays = int(a[a.index("--budget") + 1]) if "--budget" in a else None
-    pos = [x for i, x in enumerate(a) if not x.startswith("-") and (i == 0 or a[i - 1] not in ("-k", "--budget"))]
-    main(pos[0], int(pos[1]) if len(pos) > 1 else 40, kern, rays)
+    skip = int(a[a.index("--skip") + 1]) if "--skip" in a else 0
+    pos = [x for i, x in enumerate(a) if not x.startswith("-") and (i == 0 or a[i - 1] not in ("-k", "--budget", "--skip"))]
+    main(pos[0], int(pos[1]) if len(pos) > 1 else 40, kern, rays, skip)

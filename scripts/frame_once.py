@@ -32,6 +32,8 @@ def main():
     ap.add_argument("--tune", type=int, default=0)
     ap.add_argument("--stats", type=int, default=0)
     ap.add_argument("--chains", type=int, default=0, help="VX_DCR_RT_CHAINS (0 = default)")
+    ap.add_argument("--sort", type=int, default=0, help="c5 experiment: order the rays on the host by (origin cell of a "
+                    "G^3 grid, direction octant) before the upload, G = this value (0 = as generated)")
     ap.add_argument("--builder", default="host", choices=["host", "device"])
     ap.add_argument("--rays", type=int, default=None)
     ap.add_argument("--ranks", type=int, default=1, help="render rank 0's strip of a frame split over this many ranks")
@@ -50,6 +52,12 @@ def main():
         lo = np.minimum.reduce([soup["v0"].min(0), soup["v1"].min(0), soup["v2"].min(0)]).astype(np.float32)
         hi = np.maximum.reduce([soup["v0"].max(0), soup["v1"].max(0), soup["v2"].max(0)]).astype(np.float32)
         rays = rt.rays_random(lo, hi, 0x5EED5EED, 0, n)
+        if args.sort:
+            g = args.sort
+            cell = np.clip(((rays["o"] - lo) / np.maximum(hi - lo, 1e-20) * g).astype(np.int64), 0, g - 1)
+            octant = (rays["d"][:, 0] < 0) * 1 + (rays["d"][:, 1] < 0) * 2 + (rays["d"][:, 2] < 0) * 4
+            key = ((cell[:, 0] * g + cell[:, 1]) * g + cell[:, 2]) * 8 + octant
+            rays = rays[np.argsort(key, kind="stable")]
         for _ in range(args.frames):
             tracer.trace(rays)
             times.append(tracer.counters()["elapsed_ns"] * 1e-6)
