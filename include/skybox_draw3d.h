@@ -46,6 +46,10 @@ extern "C" {
 #define VX_DCR_TEX_FILTER (VX_DCR_TEX_STATE_BEGIN + 4)
 #define VX_DCR_TEX_WRAP (VX_DCR_TEX_STATE_BEGIN + 5)
 #define VX_DCR_TEX_MIPOFF(lod) (VX_DCR_TEX_STATE_BEGIN + 6 + (lod))
+/* Mip levels > 0: the DCR file stores all 16 MIPOFF words and the kernel_arg_t mirror carries them, but this
+ * back-end SAMPLES LEVEL 0 ONLY -- the one call site, draw3d/kernel.cpp:160-164, passes lod = 0 to the sampler, and
+ * the apps upload level 0 alone (apps/draw3d/draw3d_app.c).  A kernel that wants trilinear lookups
+ * (sim/common/graphics.cpp:253-314 with lod > 0) is outside what this library renders. */
 #define VX_DCR_TEX_STATE_END (VX_DCR_TEX_MIPOFF(VX_TEX_LOD_MAX) + 1)
 #define VX_DCR_TEX_STATE_COUNT (VX_DCR_TEX_STATE_END - VX_DCR_TEX_STATE_BEGIN) /* 22 */
 

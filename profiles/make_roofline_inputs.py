@@ -11,13 +11,16 @@ import re
 HERE = os.path.dirname(os.path.abspath(__file__))
 # "<workload>:v<variant>" -> summary file (one frame / one ray list of that configuration)
 CAPTURES = {
-    "c3:v0": "r02_c3_wave_summary.txt", "c3:v4": "r02_c3_wave_summary.txt", "c3:v7": "r02_c3_mega_vote_summary.txt",
-    "c3:v1": "r02_c3_baseline_summary.txt", "c2:v0": "r02_c2_wave_summary.txt", "c2:v4": "r02_c2_wave_summary.txt",
-    "c5:v0": "r02_c5_vote_summary.txt", "c5:v7": "r02_c5_vote_summary.txt", "c5:v1": "r02_c5_baseline_summary.txt",
+    "c3:v0": "r02b_c3_wave_summary.txt", "c3:v4": "r02b_c3_wave_summary.txt", "c3:v7": "r02_c3_mega_vote_summary.txt",
+    "c3:v1": "r02_c3_baseline_summary.txt", "c2:v0": "r02b_c2_wave_summary.txt", "c2:v4": "r02b_c2_wave_summary.txt",
+    "c5:v0": "r02b_c5_vote_summary.txt", "c5:v7": "r02b_c5_vote_summary.txt", "c5:v1": "r02_c5_baseline_summary.txt",
     "c5:v3": "r02_c5_pool_summary.txt", "c5:v4": "r02_c5_while_summary.txt",
+    "c4:v0": "r02b_c4_wave_summary.txt", "c4:v4": "r02b_c4_wave_summary.txt",
 }
 # captures of a PART of the step (noted in the record): c5 = 16 Mi of the 64 Mi rays; c4 = the trace kernels of one of 8 sample planes
-PARTIAL = {"c5": "16 Mi of the 64 Mi rays (scripts/frame_once.py --workload c5): dram_bytes / warp_inst scale by 4 for the bench step"}
+PARTIAL = {"c5": ("16 Mi of the 64 Mi rays (scripts/frame_once.py --workload c5): dram_bytes / warp_inst scale by 4 for the bench step", 0.25),
+           "c4": ("the three trace kernels of the frame (all 8 sample planes in one pass); the two shading passes and the "
+                  "combine, ~8 % of the frame, are not in the capture", 1.0)}
 UNIT = {"us": 1e-6, "ms": 1e-3, "s": 1.0, "ns": 1e-9, "byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "": 1, "inst": 1, "%": 1}
 
 
@@ -53,8 +56,7 @@ def main():
         }
         wl = key.split(":")[0]
         if wl in PARTIAL:
-            rec["partial"] = PARTIAL[wl]
-            rec["step_fraction"] = 0.25
+            rec["partial"], rec["step_fraction"] = PARTIAL[wl]
         out[key] = rec
     with open(os.path.join(HERE, "roofline_inputs.json"), "w") as f:
         json.dump(out, f, indent=1, sort_keys=True)

@@ -115,7 +115,7 @@ struct vx_device {
                                         1 = never (a pixel's samples run sequentially in one lane), 2 = always */
 #define VX_DCR_RT_CHAINS  0x809 /* wavefront pipeline: independent chains a frame is split into so that the tail of one
                                    chain's trace kernel overlaps the other chain's next kernel (0 = default: 2 for
-                                   passes of >= 2^21 jobs, else 1; 1..4 forced)                                      */
+                                   passes of >= 1.5 M jobs, else 1; 1..4 forced)                                      */
 #define VX_DCR_RT_PASS_JOBS 0x80A /* wavefront pipeline: jobs (pixels x samples) one pass may hold, 0 = default 2^27; a frame
                                     with more runs as several passes over sample ranges (tests force this path)      */
 #define VX_DCR_RT_REPACK  0x808 /* BVH2 -> Node4: 0 = on the device (rt_repack_device.cu), 1 = on the host (rt_repack.cpp), A/B */
