@@ -130,8 +130,9 @@ int vx_cuda_frame_gather(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h strip
                          uint32_t height, uint32_t rows_per_block, uint32_t root);
 
 /* The same exchange for ranks that render into FULL-SIZE frame buffers with their row blocks at the final positions
- * (the raster path deals 32-row tile rows round-robin): the root receives every other rank's blocks straight into
- * its own `frame` at the same offsets; no staging, no de-interleave.  Every rank passes its full-size buffer. */
+ * (the raster path deals 32-row tile rows round-robin): a sending rank packs its blocks into one strip and sends it
+ * as one message, the root scatters the received strips to their rows of its own `frame`; its own rows never move.
+ * Every rank passes its full-size buffer. */
 int vx_cuda_frame_gather_inplace(vx_device_h hdevice, vx_comm_h hcomm, vx_buffer_h frame, uint32_t width, uint32_t height,
                                  uint32_t rows_per_block, uint32_t root);
 
