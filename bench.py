@@ -79,37 +79,87 @@ def parse():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons while the timed region runs (B200_PROFILING.md)."""
+    """SM clock + throttle reasons while the timed region runs (B200_PROFILING.md).  NVML is polled from a thread every
+    ~2 ms with a time stamp per sample (the timed region of a 20-step run is ~30 ms: `nvidia-smi -lms 100`, used in
+    round 1, returned no sample inside it at N = 8); the record describes the samples that fall inside the window
+    the caller marks with `window(t0, t1)` (time.perf_counter values around the timed loop).  Falls back to
+    nvidia-smi when NVML is not importable."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        self.idx, self.rows, self.proc = gpu_index, [], None
+        self.idx, self.rows, self.proc, self.th = gpu_index, [], None, None
+        self.t0 = self.t1 = None
+        self.nvml = None
+        self.stop_flag = False
+
+    def window(self, t0, t1):
+        self.t0, self.t1 = t0, t1
 
     def start(self):
         try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                import torch
+                uuid = str(torch.cuda.get_device_properties(self.idx).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:  # noqa: BLE001 -- no torch / no uuid: physical index (no CUDA_VISIBLE_DEVICES remapping)
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(self.idx)
+            self.nvml = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
+        except Exception:  # noqa: BLE001
+            self.nvml = None
+        try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20", "-i",
                  str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._pump, daemon=True)
             self.th.start()
         except OSError:
             self.proc = None
 
+    def _poll(self):
+        n = self.nvml
+        names = (("hw_slowdown", n.nvmlClocksThrottleReasonHwSlowdown), ("hw_thermal_slowdown", n.nvmlClocksThrottleReasonHwThermalSlowdown),
+                 ("sw_thermal_slowdown", n.nvmlClocksThrottleReasonSwThermalSlowdown), ("sw_power_cap", n.nvmlClocksThrottleReasonSwPowerCap))
+        while not self.stop_flag:
+            try:
+                t = time.perf_counter()
+                sm = float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
+                mask = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.rows.append((t, sm, [k for k, bit in names if mask & bit]))
+            except Exception:  # noqa: BLE001
+                break
+            time.sleep(0.002)
+
     def _pump(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.th.join(timeout=2)
+            rows = self.rows
+            inside = [r for r in rows if self.t0 is not None and self.t0 <= r[0] <= self.t1]
+            used, scope = (inside, "inside the timed region") if inside else (rows, "whole run (no sample fell inside the timed region)")
+            sm = [r[1] for r in used]
+            reasons = sorted({k for r in used for k in r[2]})
+            return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz, "samples": len(sm),
+                    "samples_total": len(rows), "scope": scope, "source": "NVML polled every ~2 ms", "reasons": reasons}
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
         self.th.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for _, r in self.rows:
             try:
                 sm.append(float(r[1])); mx.append(float(r[2]))
             except (ValueError, IndexError):
@@ -119,7 +169,7 @@ class ClockSampler:
                     reasons.add(n)
         busy = sorted(sm)[len(sm) // 2:] if sm else []  # upper half = samples under load
         return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "source": "nvidia-smi -lms 20", "reasons": sorted(reasons)}
 
 
 def weak_frame(w0, h0, n):
@@ -521,6 +571,9 @@ def native_arm(args, wl, steps, solo=False, sample_clocks=True):
         c = tracer.counters()
         return c["rays_primary"] + c["rays_shadow"] + c["rays_bounce"], c
 
+    sampler = ClockSampler(local) if sample_clocks else None
+    if sampler:
+        sampler.start()  # polling runs through the warm-up as well: it is in steady state when the timed region begins
     # ---- warm-up --------------------------------------------------------------------------
     for _ in range(max(args.warmup, 3)):
         launch()
@@ -530,9 +583,6 @@ def native_arm(args, wl, steps, solo=False, sample_clocks=True):
     rays_per_step, ctr = step_rays()
 
     # ---- timed: K steps, device time on the launch stream, L2 flushed before each ------------
-    sampler = ClockSampler(local) if sample_clocks else None
-    if sampler:
-        sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     barrier()
     t_wall = time.perf_counter()
@@ -546,7 +596,10 @@ def native_arm(args, wl, steps, solo=False, sample_clocks=True):
                 gather()
             b.record(stream)
     barrier()
-    t_wall = time.perf_counter() - t_wall
+    t_end = time.perf_counter()
+    if sampler:
+        sampler.window(t_wall, t_end)
+    t_wall = t_end - t_wall
     clocks = sampler.stop() if sampler else None
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
     kern_ns = dev.mpm_query(vx.VX_CSR_RT_ELAPSED_NS)  # vx_start..end of the last step, without gather

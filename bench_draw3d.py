@@ -174,6 +174,8 @@ def native_arm(args, ClockSampler, load_peaks):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    sampler.start()  # polls through the warm-up too; the record describes the samples inside the timed window
     with torch.cuda.stream(stream):
         for _ in range(warm):
             clear_dev()
@@ -182,11 +184,10 @@ def native_arm(args, ClockSampler, load_peaks):
                 gather()
     barrier()
 
-    sampler = ClockSampler(local)
-    sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
           for _ in range(K)]
     barrier()
+    t_begin = time.perf_counter()
     with torch.cuda.stream(stream):
         for a, b, c in ev:
             clear_dev()
@@ -198,6 +199,7 @@ def native_arm(args, ClockSampler, load_peaks):
                 gather()
             c.record(stream)
     barrier()
+    sampler.window(t_begin, time.perf_counter())
     clocks = sampler.stop()
     dev_ms = sum(a.elapsed_time(c) for a, b, c in ev)
     kern_ms = sum(a.elapsed_time(b) for a, b, c in ev) / K  # the draws of one frame, without the gather

@@ -117,7 +117,8 @@ static int wide_prepare(vx_device* dev, RtState* st, const kernel_arg_t& a) {
     VX_CUDA_OK(cudaMalloc(&d_n4, n4.size() * sizeof(Node4)));
     VX_CUDA_OK(cudaMemcpyAsync(d_n4, n4.data(), n4.size() * sizeof(Node4), cudaMemcpyHostToDevice, dev->stream));
     VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
-  } else if (repack_bvh4_device(dev->stream, d_n2, a.num_nodes, d_tr, a.num_tris, &d_n4, &count4, &depth) != 0) {
+  } else if (repack_bvh4_device(dev->stream, d_n2, a.num_nodes, d_tr, a.num_tris, &d_n4, &count4, &depth,
+                                vx_dev_dcr(dev, VX_DCR_RT_REPACK) == 2) != 0) {
     // the repack where the data is: once per scene, level by level (rt_repack_device.cu)
     fprintf(stderr, "[VXDRV] raytrace: malformed BVH2 (child / triangle range out of bounds, or a leaf with more "
                     "than %d triangles)\n", SRT_MAX_LEAF_TRIS);

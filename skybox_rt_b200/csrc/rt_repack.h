@@ -38,8 +38,9 @@ int repack_bvh4(const srt_bvh2_node_t* nodes2, uint32_t num_nodes, const srt_tri
 
 // The same on the device (rt_repack_device.cu): d_nodes2 / d_tris are device pointers, *d_out is cudaMalloc'ed and
 // owned by the caller.  Byte-identical to repack_bvh4's output.
+// per_level: the round-1 schedule (five launches and a read-back per tree level) instead of one cooperative launch.
 int repack_bvh4_device(cudaStream_t stream, const srt_bvh2_node_t* d_nodes2, uint32_t num_nodes,
                        const srt_tri_rec_t* d_tris, uint32_t num_tris, float4** d_out, uint32_t* num_nodes4,
-                       uint32_t* max_depth);
+                       uint32_t* max_depth, bool per_level = false);
 
 }  // namespace srt

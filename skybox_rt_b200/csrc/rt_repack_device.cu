@@ -8,8 +8,13 @@
 // index.  Breadth-first order makes that index "end of this level + number of inner entries of the wide nodes before
 // me in this level + my own earlier slots" -- a prefix sum.  So, per level: count (thread / wide node) -> scan ->
 // emit (thread / wide node: planes rounded outward in double precision exactly as the host does, refs, and src[] of
-// the next level).  One 8-byte read-back per level tells the host how wide the next level is; a 1 M-triangle SAH
-// tree has 12 levels.
+// the next level).
+// Round 1 ran that as five launches and one 8-byte read-back PER LEVEL (a 1 M-triangle SAH tree has 12-15 levels:
+// 548 us of 30+ launches, launch-bound on the narrow top levels).  Now it is ONE cooperative launch
+// (repack_all_kernel): a persistent grid walks the levels with two grid-wide barriers each -- count + CTA-local
+// scan | barrier | CTA bases from the block sums, emit | barrier -- and the host reads back one 16-byte record at
+// the end.  The level-per-launch path stays as VX_DCR_RT_REPACK = 2 for A/B; all three produce the same bytes.
+#include <cooperative_groups.h>
 #include <math.h>
 #include <stdio.h>
 
@@ -105,13 +110,11 @@ __global__ void __launch_bounds__(128) repack_count_kernel(const srt_bvh2_node_t
 __device__ __forceinline__ double dmin(double a, double b) { return b < a ? b : a; }  // std::min
 __device__ __forceinline__ double dmax(double a, double b) { return a < b ? b : a; }  // std::max
 
-__global__ void __launch_bounds__(128) repack_emit_kernel(const srt_bvh2_node_t* __restrict__ n2, uint32_t num_nodes,
-                                                          uint32_t num_tris, const srt_tri_rec_t* __restrict__ tris,
-                                                          uint32_t* __restrict__ src, uint32_t begin, uint32_t n,
-                                                          const uint2* __restrict__ offset, uint32_t next_begin,
-                                                          uint32_t capacity, double delta, float4* __restrict__ out) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+// wide node begin + i: its Node4 record, and src[] of the wide nodes its inner entries become (first one = `next`)
+__device__ __forceinline__ void emit_node(const srt_bvh2_node_t* __restrict__ n2, uint32_t num_nodes, uint32_t num_tris,
+                                          const srt_tri_rec_t* __restrict__ tris, uint32_t* __restrict__ src,
+                                          uint32_t begin, uint32_t i, uint32_t next, uint32_t capacity, double delta,
+                                          float4* __restrict__ out) {
   Ent ch[4];
   int count;
   if (collapse4(n2, num_nodes, num_tris, src[begin + i], ch, count) != 0) return;  // flagged by the count pass
@@ -123,7 +126,6 @@ __global__ void __launch_bounds__(128) repack_emit_kernel(const srt_bvh2_node_t*
     for (int k = 0; k < 6; ++k) plane[k][s] = (k & 1) ? -__int_as_float(0x7f800000) : __int_as_float(0x7f800000);
     ref[s] = kEmptyRef;
   }
-  uint32_t next = next_begin + offset[i].x;
   for (int s = 0; s < count; ++s) {
     double lo[3], hi[3];
     if (ch[s].tri) {
@@ -159,12 +161,96 @@ __global__ void __launch_bounds__(128) repack_emit_kernel(const srt_bvh2_node_t*
   o[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 
+__global__ void __launch_bounds__(128) repack_emit_kernel(const srt_bvh2_node_t* __restrict__ n2, uint32_t num_nodes,
+                                                          uint32_t num_tris, const srt_tri_rec_t* __restrict__ tris,
+                                                          uint32_t* __restrict__ src, uint32_t begin, uint32_t n,
+                                                          const uint2* __restrict__ offset, uint32_t next_begin,
+                                                          uint32_t capacity, double delta, float4* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  emit_node(n2, num_nodes, num_tris, tris, src, begin, i, next_begin + offset[i].x, capacity, delta, out);
+}
+
+// ---- the whole repack in one cooperative launch ---------------------------------------------------------------
+struct RepackCtl {
+  uint32_t end, levels, error, pad;
+};
+
+__device__ __forceinline__ uint32_t count_inner(const srt_bvh2_node_t* n2, uint32_t num_nodes, uint32_t num_tris,
+                                                uint32_t root, uint32_t* error) {
+  Ent ch[4];
+  int count;
+  if (collapse4(n2, num_nodes, num_tris, root, ch, count) != 0) {
+    atomicOr(error, 1u);
+    return 0u;
+  }
+  uint32_t k = 0;
+  for (int s = 0; s < count; ++s) k += ch[s].tri ? 0u : 1u;
+  return k;
+}
+
+// Persistent grid (#SM x resident CTAs).  Every level's wide nodes [begin, end) are dealt to the CTAs in contiguous
+// chunks, so that "inner entries of the wide nodes before me" = the sums of the CTAs before mine + a CTA-local scan.
+__global__ void __launch_bounds__(kScanThreads)
+repack_all_kernel(const srt_bvh2_node_t* __restrict__ n2, uint32_t num_nodes, uint32_t num_tris,
+                  const srt_tri_rec_t* __restrict__ tris, uint32_t* __restrict__ src, uint32_t* __restrict__ local_off,
+                  uint32_t* __restrict__ block_sum, uint32_t capacity, double delta, float4* __restrict__ out,
+                  RepackCtl* __restrict__ ctl) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  const uint32_t nb = gridDim.x, b = blockIdx.x;
+  uint32_t begin = 0, end = 1, levels = 0;
+  while (begin < end) {
+    const uint32_t n = end - begin;
+    ++levels;
+    const uint32_t chunk = (n + nb - 1) / nb;
+    const uint32_t c0 = b * chunk < n ? b * chunk : n, c1 = c0 + chunk < n ? c0 + chunk : n;
+    // count + CTA-local exclusive scan (CTA-uniform trip count)
+    uint32_t carry = 0;
+    for (uint32_t t0 = c0; t0 < c1; t0 += kScanThreads) {
+      const uint32_t i = t0 + threadIdx.x;
+      const uint32_t k = i < c1 ? count_inner(n2, num_nodes, num_tris, src[begin + i], &ctl->error) : 0u;
+      uint2 total;
+      const uint2 ex = cta_exclusive(make_uint2(k, 0u), &total);
+      if (i < c1) local_off[begin + i] = carry + ex.x;
+      carry += total.x;
+    }
+    if (threadIdx.x == 0) block_sum[b] = carry;
+    grid.sync();
+    // my CTA's base and the level's total from the block sums
+    uint2 part = make_uint2(0u, 0u);
+    for (uint32_t j = threadIdx.x; j < nb; j += kScanThreads) {
+      const uint32_t v = __ldcg(block_sum + j);
+      part.y += v;
+      if (j < b) part.x += v;
+    }
+    uint2 sums;
+    cta_exclusive(part, &sums);
+    const uint32_t level_total = sums.y;
+    const bool bad = __ldcg(&ctl->error) != 0u || (uint64_t)end + level_total > capacity;  // malformed, or a cycle
+    if (!bad)
+      for (uint32_t i = c0 + threadIdx.x; i < c1; i += kScanThreads)
+        emit_node(n2, num_nodes, num_tris, tris, src, begin, i, end + sums.x + local_off[begin + i], capacity, delta, out);
+    if (bad) {
+      if (b == 0 && threadIdx.x == 0) ctl->error = 1u;
+      break;  // every thread of the grid takes this branch together
+    }
+    grid.sync();  // src[] of the next level is complete, block_sum may be overwritten
+    begin = end;
+    end += level_total;
+  }
+  if (b == 0 && threadIdx.x == 0) {
+    ctl->end = end;
+    ctl->levels = levels;
+  }
+}
+
 }  // namespace
 
 // d_n2 / d_tris: the app's buffers.  On success *d_out (cudaMalloc'ed, owned by the caller) holds *num_nodes4
 // Node4 records and *depth the number of wide levels.  -1: malformed BVH2 (as repack_bvh4) or out of memory.
 int repack_bvh4_device(cudaStream_t s, const srt_bvh2_node_t* d_n2, uint32_t num_nodes, const srt_tri_rec_t* d_tris,
-                       uint32_t num_tris, float4** d_out, uint32_t* num_nodes4, uint32_t* depth) {
+                       uint32_t num_tris, float4** d_out, uint32_t* num_nodes4, uint32_t* depth, bool per_level) {
   *d_out = nullptr;
   if (!d_n2 || !d_tris || num_nodes == 0 || num_tris == 0 || num_tris > 0x7FFFFFFFu) return -1;
   srt_bvh2_node_t root;
@@ -194,6 +280,38 @@ int repack_bvh4_device(cudaStream_t s, const srt_bvh2_node_t* d_n2, uint32_t num
   }
   int rc = -1;
   uint32_t begin = 0, end = 1, levels = 0;
+  if (!per_level) {
+    // one cooperative launch; `inner` serves as the CTA-local offsets, `offset` as the block sums, `totals` as the
+    // control record (16 bytes)
+    do {
+      int dev_id = 0, per_sm = 0, sms = 0;
+      if (cudaGetDevice(&dev_id) != cudaSuccess ||
+          cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev_id) != cudaSuccess ||
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, repack_all_kernel, kScanThreads, 0) != cudaSuccess ||
+          per_sm <= 0)
+        break;
+      uint64_t grid = (uint64_t)sms * (uint64_t)per_sm;  // all CTAs resident: a cooperative launch requires it
+      if (grid > capacity) grid = capacity;              // (also keeps the block sums inside the `offset` allocation)
+      if (cudaMemsetAsync(src, 0, 4, s) != cudaSuccess || cudaMemsetAsync(totals, 0, 16, s) != cudaSuccess) break;
+      RepackCtl* ctl = reinterpret_cast<RepackCtl*>(totals);
+      uint32_t* block_sum = reinterpret_cast<uint32_t*>(offset);  // capacity * 8 bytes >= grid * 4 (grid <= capacity)
+      const srt_bvh2_node_t* a_n2 = d_n2;
+      const srt_tri_rec_t* a_tris = d_tris;
+      uint32_t a_nodes = num_nodes, a_ntris = num_tris, a_cap = capacity;
+      double a_delta = delta;
+      void* args[] = {&a_n2, &a_nodes, &a_ntris, &a_tris, &src, &inner, &block_sum, &a_cap, &a_delta, &out, &ctl};
+      if (cudaLaunchCooperativeKernel((const void*)repack_all_kernel, dim3((unsigned)grid), dim3(kScanThreads), args, 0, s) !=
+          cudaSuccess)
+        break;
+      RepackCtl h;
+      if (cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess)
+        break;
+      if (h.error) break;
+      end = h.end;
+      levels = h.levels;
+      rc = 0;
+    } while (0);
+  } else
   do {
     if (cudaMemsetAsync(src, 0, 4, s) != cudaSuccess || cudaMemsetAsync(error, 0, 4, s) != cudaSuccess) break;
     bool ok = true;

@@ -169,7 +169,7 @@ def test_errors(native):
 # ---------------------------------------------------------------- BVH2 -> Node4 repack on the device
 def _node4_images(make_tracer, w=48, h=32):
     out = []
-    for mode in (1, 0):  # host repack (rt_repack.cpp), device repack (rt_repack_device.cu)
+    for mode in (1, 0, 2):  # host repack (rt_repack.cpp), device repack in one cooperative launch, device repack per level
         with make_tracer() as t:
             t.dev.dcr_write(vx.VX_DCR_RT_REPACK, mode)
             fb = t.render(rt.make_arg(w, h, 2, spp=1, seed=3, scene="terrain"))
@@ -187,10 +187,11 @@ def test_device_repack_equals_host_repack(native, builder, quads):
         make = lambda: rt.RayTracer(nodes, tris)
     else:
         make = lambda: rt.RayTracer(soup=soup)
-    (host_img, host_fb), (dev_img, dev_fb) = _node4_images(make)
+    (host_img, host_fb), (dev_img, dev_fb), (lvl_img, lvl_fb) = _node4_images(make)
     assert len(host_img) == len(dev_img) and len(host_img) % 128 == 0 and len(host_img) > 0
     assert host_img == dev_img, f"{sum(a != b for a, b in zip(host_img, dev_img))} bytes differ"
-    assert np.array_equal(host_fb, dev_fb)
+    assert host_img == lvl_img
+    assert np.array_equal(host_fb, dev_fb) and np.array_equal(host_fb, lvl_fb)
 
 
 def test_device_repack_refuses_what_the_host_repack_refuses(native):
@@ -204,7 +205,7 @@ def test_device_repack_refuses_what_the_host_repack_refuses(native):
     n = nodes.copy(); n["left_first"][leaf] = len(tris); bad.append(n)             # triangle range out of bounds
     inner = int(np.nonzero(nodes["count"] == 0)[0][3])
     n = nodes.copy(); n["left_first"][inner] = 1; bad.append(n)                    # a cycle
-    for mode in (0, 1):
+    for mode in (0, 1, 2):
         for k, n in enumerate(bad):
             with rt.RayTracer(n, tris) as t:
                 t.dev.dcr_write(vx.VX_DCR_RT_REPACK, mode)
