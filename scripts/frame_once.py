@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--tune", type=int, default=0)
     ap.add_argument("--stats", type=int, default=0)
     ap.add_argument("--chains", type=int, default=0, help="VX_DCR_RT_CHAINS (0 = default)")
+    ap.add_argument("--unfused", type=int, default=0, help="VX_DCR_RT_FUSE_BOUNCE (1 = separate K4 / K5 launches)")
     ap.add_argument("--sort", type=int, default=0, help="c5 experiment: order the rays on the host by (origin cell of a "
                     "G^3 grid, direction octant) before the upload, G = this value (0 = as generated)")
     ap.add_argument("--builder", default="host", choices=["host", "device"])
@@ -46,6 +47,7 @@ def main():
     dev.dcr_write(vx.VX_DCR_RT_KEEP_ACTIVE, args.tune)
     dev.dcr_write(vx.VX_DCR_RT_STATS, args.stats)
     dev.dcr_write(vx.VX_DCR_RT_CHAINS, args.chains)
+    dev.dcr_write(vx.VX_DCR_RT_FUSE_BOUNCE, args.unfused)
     times = []
     if "rays" in cfg:
         n = args.rays or cfg["rays"]

@@ -53,7 +53,7 @@ struct RtState {
   WaveCtl* d_wave_ctl;             // kMaxChains control blocks
   cudaStream_t chain_stream[3];    // the extra chains of a frame run here (the first one on the device stream)
   cudaEvent_t chain_fork, chain_join[3];
-  int wave_blocks_per_sm[18];      // occupancy per (stage, scheduler, stats) instantiation
+  int wave_blocks_per_sm[24];      // occupancy per (stage, scheduler, stats) instantiation
 };
 
 static int rt_state(vx_device* dev, RtState** out) {
@@ -259,14 +259,21 @@ static int wave_chain(vx_device* dev, RtState* st, const kernel_arg_t& a, const 
   if (wave_trace<0, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
   rt_wave_shade1_kernel<<<blocks, 256, 0, s>>>(a, tris, wb, rows, jobs, plane_jobs, s_base);
   *launches += 2;
-  if (a.mode >= SRT_MODE_SHADOW) {
-    if (wave_trace<1, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
+  const bool fused = a.mode >= SRT_MODE_BOUNCE && vx_dev_dcr(dev, VX_DCR_RT_FUSE_BOUNCE) == 0;
+  if (fused) {
+    // K3': shadow + bounce queues, bounce hits shaded in-lane and their shadow rays traced by the same lane
+    if (wave_trace<3, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
     *launches += 1;
-  }
-  if (a.mode >= SRT_MODE_BOUNCE) {
-    rt_wave_shade2_kernel<<<blocks < sm_blocks ? blocks : sm_blocks, 256, 0, s>>>(a, tris, wb);
-    if (wave_trace<2, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
-    *launches += 2;
+  } else {
+    if (a.mode >= SRT_MODE_SHADOW) {
+      if (wave_trace<1, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
+      *launches += 1;
+    }
+    if (a.mode >= SRT_MODE_BOUNCE) {
+      rt_wave_shade2_kernel<<<blocks < sm_blocks ? blocks : sm_blocks, 256, 0, s>>>(a, tris, wb);
+      if (wave_trace<2, SCHED, STATS>(dev, st, a, sc, wb, s, rows, jobs, plane_jobs, s_base) != 0) return -1;
+      *launches += 2;
+    }
   }
   return 0;
 }

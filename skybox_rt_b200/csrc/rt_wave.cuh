@@ -85,6 +85,11 @@ __device__ __forceinline__ uint32_t queue_slot(uint32_t* counter, bool want) {
 // STAGE 1: jobs [0, n_shadow1) = shadow rays of hit 1 (any hit)            -> path[job].y = 0 when occluded
 //          jobs [n_shadow1, n_shadow1 + n_bounce) = bounce rays (closest)  -> hit2[slot]
 // STAGE 2: shadow rays of hit 2 (any hit)                                  -> path[job].w = 0 when occluded
+// STAGE 3: stage 1 with K4 and K5 folded in (the default): a lane whose bounce ray ends shades the bounce hit itself
+//          (the arithmetic of rt_wave_shade2_kernel), writes the path state and goes on with that path's second
+//          shadow ray instead of taking a new job.  Removes a latency-bound shading pass and a trace launch that ran
+//          at 30 % warps active (its queue is short and ends in a long tail); the bounce rays are the back half of
+//          the launch's job list, so the in-lane shading runs when most advancing lanes of a warp need it.
 // Persistent: grid = #SM x resident CTAs, 32 jobs per fetch from ctl->cursor[STAGE], lanes refilled by ballot /
 // prefix popc when fewer than `tune` lanes of the warp are still traversing (run_warp, rt_wide.cuh).
 template <int STAGE, int SCHED, bool STATS>
@@ -100,8 +105,11 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
   const uint32_t W = a.dst_width, tiles_x = (W + 7u) / 8u;
   const uint32_t seed_hash = mix32(a.seed);
   const Camera cam = make_camera(a);
-  const uint32_t n_first = STAGE == 1 ? wb.ctl->n_shadow1 : 0u;
-  const uint32_t total_jobs = STAGE == 0 ? cam_jobs : (STAGE == 1 ? n_first + wb.ctl->n_bounce : wb.ctl->n_shadow2);
+  constexpr bool kStage1 = STAGE == 1 || STAGE == 3, kFused = STAGE == 3;
+  const uint32_t n_first = kStage1 ? wb.ctl->n_shadow1 : 0u;
+  const uint32_t total_jobs = STAGE == 0 ? cam_jobs : (kStage1 ? n_first + wb.ctl->n_bounce : wb.ctl->n_shadow2);
+  uint32_t n_second = 0u;  // fused: second shadow rays started by this lane
+  bool second = false;     // fused: the any-hit ray in flight is the path's second shadow ray
   Pool pool = {0u, 0u, false};
   RayState r;
   Hit best;
@@ -116,16 +124,38 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
 
   auto advance = [&]() {
     if (have_job && !cu.busy()) {
+      have_job = false;
       if (r.any) {
-        if (r.found) reinterpret_cast<float*>(wb.path + my_path)[STAGE == 1 ? 1 : 3] = 0.0f;
+        if (r.found) reinterpret_cast<float*>(wb.path + my_path)[(kStage1 && !second) ? 1 : 3] = 0.0f;
+      } else if (kFused) {
+        // the bounce hit, shaded here: rt_wave_shade2_kernel's statements on this lane's ray
+        float* p = reinterpret_cast<float*>(wb.path + my_path);
+        if (best.prim == SRT_MISS) {
+          p[3] = kBounceMissed;
+        } else {
+          const float4 r1 = __ldg(sc.tris + 3 * (size_t)best.rec + 1), r2 = __ldg(sc.tris + 3 * (size_t)best.rec + 2);
+          const Surface sf = surface_at(a, r1, r2, r.o, r.d, best.t);
+          const bool lit = sf.ndl > 0.0f;
+          p[2] = r1.w;
+          p[3] = lit ? sf.ndl : 0.0f;
+          if (lit && a.mode >= SRT_MODE_SHADOW) {
+            ++n_second;
+            second = true;
+            have_job = true;  // the lane stays on this path
+            if (STATS) stats.rays += 1;
+            ray_setup(r, sf.po, sf.ld, 0.0f, true);
+            best.t = sf.dist; best.prim = SRT_MISS; best.rec = SRT_MISS;
+            st.reset();
+            cu.go(0u);
+          }
+        }
       } else {
         const uint2 h = make_uint2(__float_as_uint(best.t), best.prim == SRT_MISS ? SRT_MISS : best.rec);
         if (STAGE == 0) wb.hit1[my_job] = h;
         else wb.hit2[my_job - n_first] = h;
       }
-      have_job = false;
     }
-    const uint32_t job = take_jobs(pool, !have_job, wb.ctl->cursor + STAGE, total_jobs);
+    const uint32_t job = take_jobs(pool, !have_job, wb.ctl->cursor + (kStage1 ? 1 : STAGE), total_jobs);
     if (job != ~0u) {
       my_job = job;
       if (STAGE == 0) {
@@ -147,6 +177,7 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
         my_path = __float_as_uint(r0.w);
         have_job = true;
         if (STATS) stats.rays += 1;
+        second = false;
         ray_setup(r, mk(r0.x, r0.y, r0.z), mk(r1.x, r1.y, r1.z), 0.0f, shadow);
         best.t = r1.w; best.prim = SRT_MISS; best.rec = SRT_MISS;
         st.reset();
@@ -156,6 +187,10 @@ rt_wave_trace_kernel(const __grid_constant__ kernel_arg_t a, const WideScene sc,
   };
   // camera rays are coherent (ALU-bound): 16-byte loads; shadow / bounce rays (L1-bound): 32-byte loads
   run_warp<SCHED, STATS, STAGE != 0>(sc, cu, r, best, st, stats, pool, have_job, advance);
+  if (kFused) {  // the combine adds ctl->n_shadow2 to the shadow-ray counter
+    n_second = __reduce_add_sync(0xffffffffu, n_second);
+    if ((threadIdx.x & 31u) == 0u && n_second) atomicAdd(&wb.ctl->n_shadow2, n_second);
+  }
   if (STATS) flush_stats(stats, counters);
 }
 

@@ -79,6 +79,24 @@ def test_wavefront_chains_do_not_change_the_frame(terrain, chains, w, h, mode, s
     assert ray_counts(c) == ray_counts(ctr)
 
 
+@pytest.mark.parametrize("variant", [vx.RT_VARIANT_WAVE, vx.RT_VARIANT_WAVE_VOTE, vx.RT_VARIANT_WAVE_DEFER])
+@pytest.mark.parametrize("w,h,mode,spp", [(320, 180, 2, 1), (201, 97, 2, 3), (64, 33, 1, 1)])
+def test_wavefront_with_separate_bounce_shading_launches(terrain, variant, w, h, mode, spp):
+    """VX_DCR_RT_FUSE_BOUNCE = 1: the bounce hit is shaded by its own pass (K4) and its shadow rays traced by their own
+    launch (K5) instead of inside the shadow + bounce trace launch -- the A/B form of the default; same frame."""
+    tracer, (onodes, otris), _ = terrain
+    tracer.dev.dcr_write(vx.VX_DCR_RT_VARIANT, variant)
+    tracer.dev.dcr_write(vx.VX_DCR_RT_FUSE_BOUNCE, 1)
+    try:
+        fb = tracer.render(rt.make_arg(w, h, mode, spp=spp, seed=99, scene="terrain"))
+        c = tracer.counters()
+    finally:
+        tracer.dev.dcr_write(vx.VX_DCR_RT_FUSE_BOUNCE, 0)
+    ref, ctr = o.render(o.make_arg(w, h, mode, spp=spp, seed=99, scene="terrain"), onodes, otris)
+    assert np.array_equal(fb, ref), f"{(fb != ref).sum()} of {fb.size} pixels differ"
+    assert ray_counts(c) == ray_counts(ctr)
+
+
 @pytest.mark.parametrize("pass_jobs", [1, 45000, 70000])  # 1 / 2 / 3 samples per pass of the 20 800-job plane
 @pytest.mark.parametrize("chains", [1, 2])
 def test_wavefront_sample_passes_keep_the_sample_order(terrain, pass_jobs, chains):
