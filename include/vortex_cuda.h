@@ -64,7 +64,11 @@ int vx_cuda_perf_totals(vx_device_h hdevice, uint64_t* out, uint32_t count);
  * srt_draw3d_binning_rank() produces for the same input (include/skybox_draw3d.h: SRT_TILEBUF_* formats,
  * rank / num_ranks tile-row dealing).  Returns 0; -1 bad arguments / out of memory / an index past the vertex
  * buffer; -2 when SRT_TILEBUF_REFERENCE's 16-bit fields would overflow.  Enqueued on the launch stream; waits
- * once for the output sizes. */
+ * once for the output sizes.
+ * tile_logsize: buffers handed to vx_start must be binned with RASTER_TILE_LOGSIZE (5, 32x32 pixels): the render
+ * kernel is built for that size like the reference's raster unit (hw/rtl/VX_config.vh:477-478) and neither tile
+ * buffer format carries the size, so a buffer binned otherwise cannot be told apart and renders wrongly.  Other
+ * sizes (1..8) exist for tooling and for the byte-for-byte comparison with graphics::Binning at its other sizes. */
 typedef struct {
   uint32_t num_tiles, num_prims;
   uint64_t num_tile_prims; /* sum of pids_count */

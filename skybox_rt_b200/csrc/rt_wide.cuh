@@ -300,29 +300,38 @@ __device__ __forceinline__ void run_warp(const WideScene& sc, Cursor& cu, RaySta
                                          Stats& stats, const Pool& pool, const bool& have_job, Advance advance) {
   if (SCHED == SCHED_WHILE) {
 #ifdef SRT_SPEC
-    // while-while with one postponed triangle per lane (speculative traversal): a lane that reaches a triangle
-    // while others of its warp still walk nodes parks it and walks on; it leaves the node loop when it meets a
-    // second triangle or runs out of nodes.  The triangle phase then tests the parked triangle of (nearly) every
-    // lane in one step.  Test order cannot change a result (closest hit = minimum over all accepted triangles).
-    uint32_t pend = kNone;
+    // while-while with up to SRT_SPEC (1..3) postponed triangles per lane (speculative traversal): a lane that reaches
+    // a triangle while others of its warp still walk nodes parks it and walks on; it leaves the node loop when its
+    // parking slots are full and it meets another triangle, or when it runs out of nodes.  Triangles come in bursts
+    // (a leaf-level Node4 holds up to four single-triangle children), so one slot does not keep a lane in the loop.
+    // The triangle phase tests the parked triangles slot by slot, each a warp-wide step.  Test order cannot change a
+    // result (closest hit = minimum over all accepted triangles).
+    uint32_t pend0 = kNone, pend1 = kNone, pend2 = kNone;
+    int np = 0;
     for (;;) {
       advance();
       if (pool.dry && !__any_sync(0xffffffffu, have_job)) return;
       for (;;) {
         while (cu.wants_node()) {
           node_step<STATS, LD256>(sc, cu, r, best.t, st, stats);
-          if (pend == kNone && cu.wants_tri()) {
-            pend = cu.ref;
+          while (np < SRT_SPEC && cu.wants_tri()) {
+            if (np == 0) pend0 = cu.ref; else if (np == 1) pend1 = cu.ref; else pend2 = cu.ref;
+            ++np;
             cu.go(pop_next(st, best.t));
           }
         }
-        if (pend != kNone) {
-          if (tri_test<STATS>(sc, pend, r, best, stats)) {
-            st.reset();
-            cu.clear();
+#pragma unroll
+        for (int k = 0; k < SRT_SPEC; ++k) {
+          if (k < np) {
+            const uint32_t t = k == 0 ? pend0 : (k == 1 ? pend1 : pend2);
+            if (tri_test<STATS>(sc, t, r, best, stats)) {  // an any-hit ray found its occluder
+              st.reset();
+              cu.clear();
+              np = 0;
+            }
           }
-          pend = kNone;
         }
+        np = 0;
         while (cu.wants_tri()) tri_step<STATS>(sc, cu, r, best, st, stats);
         if (__popc(__ballot_sync(0xffffffffu, cu.busy())) < sc.tune) break;
       }
