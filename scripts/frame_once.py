@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--tune", type=int, default=0)
     ap.add_argument("--stats", type=int, default=0)
     ap.add_argument("--chains", type=int, default=0, help="VX_DCR_RT_CHAINS (0 = default)")
+    ap.add_argument("--rotate", type=int, default=0, help="VX_DCR_RT_LBVH_ROTATE for --builder device (0 default, 1 none, k = k-1 passes)")
     ap.add_argument("--unfused", type=int, default=0, help="VX_DCR_RT_FUSE_BOUNCE (1 = separate K4 / K5 launches)")
     ap.add_argument("--sort", type=int, default=0, help="c5 experiment: order the rays on the host by (origin cell of a "
                     "G^3 grid, direction octant) before the upload, G = this value (0 = as generated)")
@@ -41,7 +42,12 @@ def main():
     args = ap.parse_args()
     cfg = CONFIGS[args.workload]
     soup = rt.scene_terrain(*cfg["quads"])
-    tracer = rt.RayTracer(soup=soup) if args.builder == "device" else rt.RayTracer(*rt.build_bvh2(soup))
+    if args.builder == "device":
+        dev0 = vx.Device()
+        dev0.dcr_write(vx.VX_DCR_RT_LBVH_ROTATE, args.rotate)
+        tracer = rt.RayTracer(soup=soup, device=dev0)
+    else:
+        tracer = rt.RayTracer(*rt.build_bvh2(soup))
     dev = tracer.dev
     dev.dcr_write(vx.VX_DCR_RT_VARIANT, args.variant)
     dev.dcr_write(vx.VX_DCR_RT_KEEP_ACTIVE, args.tune)

@@ -246,7 +246,7 @@ __device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys
 __global__ void __launch_bounds__(256) lbvh_hierarchy_kernel(const unsigned long long* __restrict__ keys, uint32_t n,
                                                              uint2* __restrict__ children, uint2* __restrict__ range,
                                                              uint32_t* __restrict__ parent_internal,
-                                                             uint32_t* __restrict__ parent_leaf) {
+                                                             uint32_t* __restrict__ parent_leaf, uint32_t* __restrict__ count) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x, N = (int)n;
   if (i >= N - 1) return;
   const int d = delta(keys, N, i, i + 1) - delta(keys, N, i, i - 1) >= 0 ? 1 : -1;
@@ -269,6 +269,7 @@ __global__ void __launch_bounds__(256) lbvh_hierarchy_kernel(const unsigned long
   const uint32_t right = last == gamma + 1 ? ((uint32_t)(gamma + 1) | kLeafFlag) : (uint32_t)(gamma + 1);
   children[i] = make_uint2(left, right);
   range[i] = make_uint2((uint32_t)first, (uint32_t)last);
+  count[i] = (uint32_t)(last - first + 1);
   if (left & kLeafFlag) parent_leaf[gamma] = (uint32_t)i; else parent_internal[gamma] = (uint32_t)i;
   if (right & kLeafFlag) parent_leaf[gamma + 1] = (uint32_t)i; else parent_internal[gamma + 1] = (uint32_t)i;
   if (i == 0) parent_internal[0] = 0xffffffffu;
@@ -298,6 +299,91 @@ __global__ void __launch_bounds__(256) lbvh_refit_kernel(uint32_t n, const uint2
   }
 }
 
+// ---- tree rotations: a bottom-up pass that lowers the SAH cost of the radix tree -----------------------------------
+// The radix tree splits where the Morton codes first differ -- spatial medians, ~8 % slower to trace than the host's
+// binned-SAH tree (C3).  At every internal node p = (L, R), once both subtrees are final (same arrival counters as
+// the refit), the four rotations that swap a child with a grandchild on the other side are priced by the one term
+// of the SAH cost they change, the surface area of the restructured child: R <-> L1 makes L = (R, L2), R <-> L2 makes
+// L = (L1, R), L <-> R1 makes R = (L, R2), L <-> R2 makes R = (R1, L).  The cheapest one is applied if it beats the
+// current tree (Kensler 2008 / Kopta et al. 2012).  Subtrees of <= SRT_MAX_LEAF_TRIS triangles become leaves over
+// a CONTIGUOUS run of sorted triangles in the emit, so a node is only restructured while it holds more than that
+// before and after; smaller subtrees move as a whole.  Deterministic: a node's decision depends only on its
+// finished subtree.  range[] is stale for restructured nodes afterwards; count[] is kept right and is what the
+// emit uses.
+__device__ __forceinline__ Box load_box(const Box* leaf_box, const Box* node_box, uint32_t ref) {
+  const volatile Box* b = (ref & kLeafFlag) ? leaf_box + (ref & ~kLeafFlag) : node_box + ref;
+  Box r;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { r.lo[k] = b->lo[k]; r.hi[k] = b->hi[k]; }
+  return r;
+}
+__device__ __forceinline__ Box unite(const Box& a, const Box& b) {
+  Box u;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { u.lo[k] = fminf(a.lo[k], b.lo[k]); u.hi[k] = fmaxf(a.hi[k], b.hi[k]); }
+  return u;
+}
+__device__ __forceinline__ float half_area(const Box& b) {
+  const float dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+  return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void __launch_bounds__(256) lbvh_rotate_kernel(uint32_t n, uint2* children, uint32_t* parent_internal,
+                                                          uint32_t* parent_leaf, const Box* __restrict__ leaf_box,
+                                                          Box* node_box, uint32_t* count, uint32_t* __restrict__ arrived) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  volatile uint2* vchildren = children;
+  volatile uint32_t* vcount = count;
+  auto cnt = [&](uint32_t ref) -> uint32_t { return (ref & kLeafFlag) ? 1u : vcount[ref]; };
+  auto set_parent = [&](uint32_t ref, uint32_t q) {
+    if (ref & kLeafFlag) parent_leaf[ref & ~kLeafFlag] = q; else parent_internal[ref] = q;
+  };
+  uint32_t p = parent_leaf[i];
+  while (p != 0xffffffffu) {
+    __threadfence();  // this thread's stores before the flag
+    if (atomicAdd(arrived + p, 1u) == 0u) return;
+    __threadfence();  // the sibling subtree's stores after the flag
+    const uint32_t L = vchildren[p].x, R = vchildren[p].y;
+    const Box bl = load_box(leaf_box, node_box, L), br = load_box(leaf_box, node_box, R);
+    const uint32_t nl = cnt(L), nr = cnt(R);
+    float best = 0.0f;
+    int pick = 0;
+    Box nb = bl;
+    uint32_t l1 = 0, l2 = 0, r1 = 0, r2 = 0;
+    if (!(L & kLeafFlag) && nl > SRT_MAX_LEAF_TRIS) {
+      l1 = vchildren[L].x; l2 = vchildren[L].y;
+      const float old = half_area(bl);
+      const Box a = unite(br, load_box(leaf_box, node_box, l2));  // R <-> L1
+      if (nr + cnt(l2) > SRT_MAX_LEAF_TRIS && old - half_area(a) > best) { best = old - half_area(a); pick = 1; nb = a; }
+      const Box b = unite(load_box(leaf_box, node_box, l1), br);  // R <-> L2
+      if (cnt(l1) + nr > SRT_MAX_LEAF_TRIS && old - half_area(b) > best) { best = old - half_area(b); pick = 2; nb = b; }
+    }
+    if (!(R & kLeafFlag) && nr > SRT_MAX_LEAF_TRIS) {
+      r1 = vchildren[R].x; r2 = vchildren[R].y;
+      const float old = half_area(br);
+      const Box a = unite(bl, load_box(leaf_box, node_box, r2));  // L <-> R1
+      if (nl + cnt(r2) > SRT_MAX_LEAF_TRIS && old - half_area(a) > best) { best = old - half_area(a); pick = 3; nb = a; }
+      const Box b = unite(load_box(leaf_box, node_box, r1), bl);  // L <-> R2
+      if (cnt(r1) + nl > SRT_MAX_LEAF_TRIS && old - half_area(b) > best) { best = old - half_area(b); pick = 4; nb = b; }
+    }
+    if (pick == 1) {
+      children[L] = make_uint2(R, l2); children[p] = make_uint2(L, l1);
+      count[L] = nr + cnt(l2); node_box[L] = nb; set_parent(R, L); set_parent(l1, p);
+    } else if (pick == 2) {
+      children[L] = make_uint2(l1, R); children[p] = make_uint2(L, l2);
+      count[L] = cnt(l1) + nr; node_box[L] = nb; set_parent(R, L); set_parent(l2, p);
+    } else if (pick == 3) {
+      children[R] = make_uint2(L, r2); children[p] = make_uint2(r1, R);
+      count[R] = nl + cnt(r2); node_box[R] = nb; set_parent(L, R); set_parent(r1, p);
+    } else if (pick == 4) {
+      children[R] = make_uint2(r1, L); children[p] = make_uint2(r2, R);
+      count[R] = cnt(r1) + nl; node_box[R] = nb; set_parent(L, R); set_parent(r2, p);
+    }
+    p = parent_internal[p];
+  }
+}
+
 // ---- emit: the flat BVH2.  Children of radix node k at nodes 1 + 2k, 2 + 2k; subtrees of <= 4 triangles = leaves.
 __device__ __forceinline__ void put_node(srt_bvh2_node_t* out, const Box& b, uint32_t left_first, uint32_t count) {
   float4* o = reinterpret_cast<float4*>(out);
@@ -306,12 +392,12 @@ __device__ __forceinline__ void put_node(srt_bvh2_node_t* out, const Box& b, uin
 }
 
 __global__ void __launch_bounds__(256) lbvh_emit_kernel(uint32_t n, const uint2* __restrict__ children,
-                                                        const uint2* __restrict__ range, const Box* __restrict__ leaf_box,
+                                                        const uint2* __restrict__ range, const uint32_t* __restrict__ count,
+                                                        const Box* __restrict__ leaf_box,
                                                         const Box* __restrict__ node_box, srt_bvh2_node_t* __restrict__ nodes) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n - 1) return;
-  const uint2 r = range[k];
-  const uint32_t size = r.y - r.x + 1;
+  const uint32_t size = count[k];  // range[] is only trusted for subtrees that become leaves (never restructured)
   if (k == 0) {
     if (size <= SRT_MAX_LEAF_TRIS) put_node(nodes, node_box[0], 0u, size);
     else put_node(nodes, node_box[0], 1u, 0u);
@@ -326,9 +412,8 @@ __global__ void __launch_bounds__(256) lbvh_emit_kernel(uint32_t n, const uint2*
       const uint32_t leaf = ch[s] & ~kLeafFlag;
       put_node(out, leaf_box[leaf], leaf, 1u);
     } else {
-      const uint2 cr = range[ch[s]];
-      const uint32_t csize = cr.y - cr.x + 1;
-      if (csize <= SRT_MAX_LEAF_TRIS) put_node(out, node_box[ch[s]], cr.x, csize);
+      const uint32_t csize = count[ch[s]];
+      if (csize <= SRT_MAX_LEAF_TRIS) put_node(out, node_box[ch[s]], range[ch[s]].x, csize);
       else put_node(out, node_box[ch[s]], 1u + 2u * ch[s], 0u);
     }
   }
@@ -381,7 +466,7 @@ extern "C" int vx_cuda_rt_build_lbvh(vx_device_h hdevice, vx_buffer_h hsoup, uin
   tmp.plan<uint32_t>(8); tmp.plan<uint32_t>(n);
   const size_t head = tmp.planned;  // scene bounds + arrival flags: initialised below
   tmp.plan<unsigned long long>(npow2); tmp.plan<Box>(n); tmp.plan<Box>(n); tmp.plan<uint2>(n); tmp.plan<uint2>(n);
-  tmp.plan<uint32_t>(n); tmp.plan<uint32_t>(n);
+  tmp.plan<uint32_t>(n); tmp.plan<uint32_t>(n); tmp.plan<uint32_t>(n);
   if (!tmp.commit()) {
     cudaGetLastError();
     fprintf(stderr, "[VXDRV] lbvh build: out of device memory\n");
@@ -397,6 +482,10 @@ extern "C" int vx_cuda_rt_build_lbvh(vx_device_h hdevice, vx_buffer_h hsoup, uin
   uint2* range = tmp.take<uint2>(n);
   uint32_t* parent_internal = tmp.take<uint32_t>(n);
   uint32_t* parent_leaf = tmp.take<uint32_t>(n);
+  uint32_t* count = tmp.take<uint32_t>(n);
+  // VX_DCR_RT_LBVH_ROTATE: 0 = default (2 rotation passes), k > 0 = k - 1 passes (1 = the plain radix tree)
+  const uint32_t rot_dcr = vx_dev_dcr(dev, VX_DCR_RT_LBVH_ROTATE);
+  const uint32_t rotate_passes = rot_dcr == 0 ? 2u : (rot_dcr - 1u > 8u ? 8u : rot_dcr - 1u);
   int rc = -1;
   do {
     if (cudaMemsetAsync(tmp.base, 0, head, s) != cudaSuccess) break;
@@ -415,9 +504,15 @@ extern "C" int vx_cuda_rt_build_lbvh(vx_device_h hdevice, vx_buffer_h hsoup, uin
       if (cudaMemcpyAsync(&nodes[0].count, &one, 4, cudaMemcpyHostToDevice, s) != cudaSuccess) break;
       if (cudaStreamSynchronize(s) != cudaSuccess) break;  // `one` lives on this stack frame
     } else {
-      lbvh_hierarchy_kernel<<<blocks, 256, 0, s>>>(keys, n, children, range, parent_internal, parent_leaf);
+      lbvh_hierarchy_kernel<<<blocks, 256, 0, s>>>(keys, n, children, range, parent_internal, parent_leaf, count);
       lbvh_refit_kernel<<<blocks, 256, 0, s>>>(n, children, parent_internal, parent_leaf, leaf_box, node_box, arrived);
-      lbvh_emit_kernel<<<blocks, 256, 0, s>>>(n, children, range, leaf_box, node_box, nodes);
+      bool ok = true;
+      for (uint32_t pass = 0; pass < rotate_passes && ok; ++pass) {
+        ok = cudaMemsetAsync(arrived, 0, (size_t)n * sizeof(uint32_t), s) == cudaSuccess;
+        lbvh_rotate_kernel<<<blocks, 256, 0, s>>>(n, children, parent_internal, parent_leaf, leaf_box, node_box, count, arrived);
+      }
+      if (!ok) break;
+      lbvh_emit_kernel<<<blocks, 256, 0, s>>>(n, children, range, count, leaf_box, node_box, nodes);
     }
     if (cudaGetLastError() != cudaSuccess) break;
     rc = 0;

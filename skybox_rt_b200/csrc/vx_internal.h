@@ -120,6 +120,8 @@ struct vx_device {
                                     with more runs as several passes over sample ranges (tests force this path)      */
 #define VX_DCR_RT_FUSE_BOUNCE 0x80B /* wavefront pipeline: 0 = bounce hits shaded and their shadow rays traced inside the shadow +
                                      bounce trace launch (default), 1 = as separate launches K4 / K5 (A/B)             */
+#define VX_DCR_RT_LBVH_ROTATE 0x80C /* vx_cuda_rt_build_lbvh: SAH tree-rotation passes over the radix tree, 0 = default (2),
+                                     k > 0 = k - 1 passes (1 = none)                                               */
 #define VX_DCR_RT_REPACK  0x808 /* BVH2 -> Node4: 0 = on the device in one cooperative launch (rt_repack_device.cu), 1 = on the
                                    host (rt_repack.cpp), 2 = on the device, one set of launches per tree level (round 1); A/B */
 #define VX_DCR_RT_END     0x810

@@ -34,6 +34,7 @@ VX_DCR_RT_VARIANT, VX_DCR_RT_STATS, VX_DCR_RT_KEEP_ACTIVE, VX_DCR_RT_PREFETCH = 
 VX_DCR_RT_CHAINS = 0x809  # wavefront pipeline: chains per frame (0 = default, 1..4)
 VX_DCR_RT_PASS_JOBS = 0x80A  # wavefront pipeline: jobs per pass (0 = default 2^27)
 VX_DCR_RT_FUSE_BOUNCE = 0x80B  # wavefront pipeline: 0 = K4 / K5 folded into K3 (default), 1 = separate launches
+VX_DCR_RT_LBVH_ROTATE = 0x80C  # device BVH build: rotation passes (0 = default 2, k = k - 1 passes)
 VX_DCR_RT_REPACK = 0x808  # 0 = BVH2 -> Node4 on the device, 1 = on the host (A/B)
 VX_DCR_RT_SPLIT_SAMPLES = 0x807  # 0 = (pixel, sample) jobs when spp > 1, 1 = never, 2 = always
 RT_VARIANT_DEFAULT, RT_VARIANT_BASELINE, RT_VARIANT_WHILE, RT_VARIANT_POOL = 0, 1, 2, 3
