@@ -11,11 +11,11 @@ import re
 HERE = os.path.dirname(os.path.abspath(__file__))
 # "<workload>:v<variant>" -> summary file (one frame / one ray list of that configuration)
 CAPTURES = {
-    "c3:v0": "r02b_c3_wave_summary.txt", "c3:v4": "r02b_c3_wave_summary.txt", "c3:v7": "r02_c3_mega_vote_summary.txt",
-    "c3:v1": "r02_c3_baseline_summary.txt", "c2:v0": "r02b_c2_wave_summary.txt", "c2:v4": "r02b_c2_wave_summary.txt",
-    "c5:v0": "r02b_c5_vote_summary.txt", "c5:v7": "r02b_c5_vote_summary.txt", "c5:v1": "r02_c5_baseline_summary.txt",
+    "c3:v0": "r02c_c3_wave_summary.txt", "c3:v4": "r02c_c3_wave_summary.txt", "c3:v7": "r02_c3_mega_vote_summary.txt",
+    "c3:v1": "r02_c3_baseline_summary.txt", "c2:v0": "r02c_c2_wave_summary.txt", "c2:v4": "r02c_c2_wave_summary.txt",
+    "c5:v0": "r02c_c5_vote_summary.txt", "c5:v7": "r02c_c5_vote_summary.txt", "c5:v1": "r02_c5_baseline_summary.txt",
     "c5:v3": "r02_c5_pool_summary.txt", "c5:v4": "r02_c5_while_summary.txt",
-    "c4:v0": "r02b_c4_wave_summary.txt", "c4:v4": "r02b_c4_wave_summary.txt",
+    "c4:v0": "r02c_c4_wave_summary.txt", "c4:v4": "r02c_c4_wave_summary.txt",
 }
 # captures of a PART of the step (noted in the record): c5 = 16 Mi of the 64 Mi rays; c4 = the trace kernels of one of 8 sample planes
 PARTIAL = {"c5": ("16 Mi of the 64 Mi rays (scripts/frame_once.py --workload c5): dram_bytes / warp_inst scale by 4 for the bench step", 0.25),
