@@ -80,7 +80,8 @@ def parse():
 
 class ClockSampler:
     """SM clock + throttle reasons while the timed region runs (B200_PROFILING.md).  NVML is polled from a thread every
-    ~2 ms with a time stamp per sample (the timed region of a 20-step run is ~30 ms: `nvidia-smi -lms 100`, used in
+    ~4 ms (on rank 0 only: its record is the one that is printed, and eight processes polling the driver at once
+    showed up as launch gaps in an 8-GPU run) with a time stamp per sample (the timed region of a 20-step run is ~30 ms: `nvidia-smi -lms 100`, used in
     round 1, returned no sample inside it at N = 8); the record describes the samples that fall inside the window
     the caller marks with `window(t0, t1)` (time.perf_counter values around the timed loop).  Falls back to
     nvidia-smi when NVML is not importable."""
@@ -135,7 +136,7 @@ class ClockSampler:
                 self.rows.append((t, sm, [k for k, bit in names if mask & bit]))
             except Exception:  # noqa: BLE001
                 break
-            time.sleep(0.002)
+            time.sleep(0.004)
 
     def _pump(self):
         for line in self.proc.stdout:
@@ -151,7 +152,7 @@ class ClockSampler:
             sm = [r[1] for r in used]
             reasons = sorted({k for r in used for k in r[2]})
             return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz, "samples": len(sm),
-                    "samples_total": len(rows), "scope": scope, "source": "NVML polled every ~2 ms", "reasons": reasons}
+                    "samples_total": len(rows), "scope": scope, "source": "NVML polled every ~4 ms", "reasons": reasons}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -571,7 +572,7 @@ def native_arm(args, wl, steps, solo=False, sample_clocks=True):
         c = tracer.counters()
         return c["rays_primary"] + c["rays_shadow"] + c["rays_bounce"], c
 
-    sampler = ClockSampler(local) if sample_clocks else None
+    sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None
     if sampler:
         sampler.start()  # polling runs through the warm-up as well: it is in steady state when the timed region begins
     # ---- warm-up --------------------------------------------------------------------------

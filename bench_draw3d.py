@@ -174,8 +174,9 @@ def native_arm(args, ClockSampler, load_peaks):
             dist.barrier()
         torch.cuda.synchronize()
 
-    sampler = ClockSampler(local)
-    sampler.start()  # polls through the warm-up too; the record describes the samples inside the timed window
+    sampler = ClockSampler(local) if rank == 0 else None  # rank 0's record is the one that is printed
+    if sampler:
+        sampler.start()  # polls through the warm-up too; the record describes the samples inside the timed window
     with torch.cuda.stream(stream):
         for _ in range(warm):
             clear_dev()
@@ -199,8 +200,10 @@ def native_arm(args, ClockSampler, load_peaks):
                 gather()
             c.record(stream)
     barrier()
-    sampler.window(t_begin, time.perf_counter())
-    clocks = sampler.stop()
+    clocks = None
+    if sampler:
+        sampler.window(t_begin, time.perf_counter())
+        clocks = sampler.stop()
     dev_ms = sum(a.elapsed_time(c) for a, b, c in ev)
     kern_ms = sum(a.elapsed_time(b) for a, b, c in ev) / K  # the draws of one frame, without the gather
 
