@@ -73,6 +73,8 @@ def parse():
     ap.add_argument("--no-flush", action="store_true", help="diagnostic: keep L2 warm between steps")
     ap.add_argument("--keep-active", type=int, default=0, help="diagnostic: refill threshold DCR (0 = default)")
     ap.add_argument("--prefetch", type=int, default=0, help="diagnostic: VX_DCR_RT_PREFETCH (2 = no L2 warm-up)")
+    ap.add_argument("--unfused", type=int, default=0, help="diagnostic: VX_DCR_RT_FUSE_BOUNCE (1 = separate K4 / K5 launches)")
+    ap.add_argument("--chains", type=int, default=0, help="diagnostic: VX_DCR_RT_CHAINS (0 = default)")
     ap.add_argument("--mode", type=int, default=None, help="diagnostic: override the workload's shading mode (0/1/2)")
     ap.add_argument("--spp", type=int, default=None, help="diagnostic: override the workload's samples per pixel")
     return ap.parse_args()
@@ -453,6 +455,8 @@ def native_arm(args, wl, steps, solo=False, sample_clocks=True):
     dev.dcr_write(vx.VX_DCR_RT_KEEP_ACTIVE, args.keep_active)
     dev.dcr_write(vx.VX_DCR_RT_PREFETCH, args.prefetch)
     dev.dcr_write(vx.VX_DCR_RT_SPLIT_SAMPLES, args.split_samples)
+    dev.dcr_write(vx.VX_DCR_RT_FUSE_BOUNCE, args.unfused)
+    dev.dcr_write(vx.VX_DCR_RT_CHAINS, args.chains)
     stream = torch.cuda.ExternalStream(dev.cuda_stream(), device=torch.device("cuda", local))
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.int32, device="cuda")
     extra = []  # buffers / communicators to release with the tracer
