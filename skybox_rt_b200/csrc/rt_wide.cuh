@@ -199,12 +199,7 @@ __device__ __forceinline__ void node_step(const WideScene& sc, Cursor& cu, const
   const float kmin = fminf(fminf(k0, k1), fminf(k2, k3));
   const uint32_t c0 = __float_as_uint(rf.x), c1 = __float_as_uint(rf.y), c2 = __float_as_uint(rf.z),
                  c3 = __float_as_uint(rf.w);
-#ifdef SRT_ANYHIT_UNORDERED
-  // experiment: an any-hit ray needs no front-to-back order -- take the first hit slot, skip the distance compare
-  const bool e0 = r.any ? h0 : k0 == kmin, e1 = !e0 && (r.any ? h1 : k1 == kmin), e2 = !e0 && !e1 && (r.any ? h2 : k2 == kmin);
-#else
   const bool e0 = k0 == kmin, e1 = !e0 && k1 == kmin, e2 = !e0 && !e1 && k2 == kmin;  // lowest index wins a tie
-#endif
   uint32_t next = c3;
   next = e2 ? c2 : next;
   next = e1 ? c1 : next;
