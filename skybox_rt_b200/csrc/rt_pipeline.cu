@@ -301,7 +301,9 @@ static int wave_frame(vx_device* dev, RtState* st, const kernel_arg_t& a, const 
     const uint32_t s_count = a.spp - s_first < per_pass ? a.spp - s_first : per_pass;
     const uint32_t jobs = plane_jobs * s_count;
     const uint32_t groups = (jobs + 255u) / 256u;
-    uint32_t chains = chains_wanted ? chains_wanted : (jobs >= 1500000u ? 2u : 1u);  // shorter passes are launch-bound (C2, 2^20 jobs: 2 chains cost 3 %)
+    // one chain by default: with the bounce stage folded into K3 the launches that had the long tails are gone, and
+    // two chains measured equal on one GPU (C3, C4) and 2 % slower with the frame gather behind them (N = 2)
+    uint32_t chains = chains_wanted ? chains_wanted : 1u;
     if (chains > (uint32_t)kMaxChains) chains = kMaxChains;
     if (chains > groups) chains = groups;
     if (chains > 1u) {

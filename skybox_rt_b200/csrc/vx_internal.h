@@ -114,8 +114,8 @@ struct vx_device {
 #define VX_DCR_RT_SPLIT_SAMPLES 0x807 /* multi-sample frames as (pixel, sample) jobs + ordered resolve: 0 = when spp > 1,
                                         1 = never (a pixel's samples run sequentially in one lane), 2 = always */
 #define VX_DCR_RT_CHAINS  0x809 /* wavefront pipeline: independent chains a frame is split into so that the tail of one
-                                   chain's trace kernel overlaps the other chain's next kernel (0 = default: 2 for
-                                   passes of >= 1.5 M jobs, else 1; 1..4 forced)                                      */
+                                   chain's trace kernel overlaps the other chain's next kernel (0 = default = 1;
+                                   2..4 forced)                                      */
 #define VX_DCR_RT_PASS_JOBS 0x80A /* wavefront pipeline: jobs (pixels x samples) one pass may hold, 0 = default 2^27; a frame
                                     with more runs as several passes over sample ranges (tests force this path)      */
 #define VX_DCR_RT_FUSE_BOUNCE 0x80B /* wavefront pipeline: 0 = bounce hits shaded and their shadow rays traced inside the shadow +
