@@ -17,6 +17,7 @@
  * (torchrun, mpirun -x) every process is one rank.  The NCCL id travels through a file (SRT_COMM_ID_FILE).
  */
 #include <getopt.h>
+#include <signal.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -76,7 +77,7 @@ static void parse_args(int argc, char** argv) {
       case 'e': seed = (uint32_t)atoi(optarg); break;
       case 'o': output_file = optarg; break;
       case 'r': reference_file = optarg; break;
-      case 'g': num_gpus = (uint32_t)atoi(optarg); break;
+      case 'g': num_gpus = (uint32_t)atoi(optarg); if (num_gpus < 1 || num_gpus > 64) { show_usage(); exit(-1); } break;
       default: show_usage(); exit(c == '?' ? 0 : -1);
     }
   }
@@ -135,6 +136,7 @@ static int exchange_comm_id(const char* path, void* id) {
 /* -g N without a launcher: fork the N ranks (before anything touches CUDA) and wait for them */
 static int fork_ranks(int argc, char** argv) {
   char id_file[256], buf[32];
+  pid_t pids[64];
   uint32_t r;
   int status, rc = 0;
   (void)argc;
@@ -152,11 +154,19 @@ static int fork_ranks(int argc, char** argv) {
       execv("/proc/self/exe", argv);
       _exit(127);
     }
+    pids[r] = pid;
   }
   for (r = 0; r < num_gpus; ++r) {
-    if (wait(&status) < 0) { rc = -1; continue; }
-    if (!WIFEXITED(status)) rc = rc ? rc : -1;
-    else if (WEXITSTATUS(status) != 0) rc = rc ? rc : WEXITSTATUS(status);
+    pid_t done = wait(&status);
+    uint32_t k;
+    if (done < 0) { rc = -1; continue; }
+    for (k = 0; k < num_gpus; ++k)
+      if (pids[k] == done) pids[k] = 0;
+    if (WIFEXITED(status) && WEXITSTATUS(status) == 0) continue;
+    if (!rc) rc = WIFEXITED(status) ? WEXITSTATUS(status) : -1;
+    /* a rank that died leaves the others waiting in a collective: end exactly the processes started here */
+    for (k = 0; k < num_gpus; ++k)
+      if (pids[k] > 0) kill(pids[k], SIGTERM);
   }
   unlink(id_file);
   return rc;

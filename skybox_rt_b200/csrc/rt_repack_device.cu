@@ -280,6 +280,7 @@ int repack_bvh4_device(cudaStream_t s, const srt_bvh2_node_t* d_n2, uint32_t num
   }
   int rc = -1;
   uint32_t begin = 0, end = 1, levels = 0;
+  bool launched = false;  // the cooperative kernel ran (its verdict stands); false = it could not be launched
   if (!per_level) {
     // one cooperative launch; `inner` serves as the CTA-local offsets, `offset` as the block sums, `totals` as the
     // control record (16 bytes)
@@ -303,6 +304,7 @@ int repack_bvh4_device(cudaStream_t s, const srt_bvh2_node_t* d_n2, uint32_t num
       if (cudaLaunchCooperativeKernel((const void*)repack_all_kernel, dim3((unsigned)grid), dim3(kScanThreads), args, 0, s) !=
           cudaSuccess)
         break;
+      launched = true;
       RepackCtl h;
       if (cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess)
         break;
@@ -311,7 +313,14 @@ int repack_bvh4_device(cudaStream_t s, const srt_bvh2_node_t* d_n2, uint32_t num
       levels = h.levels;
       rc = 0;
     } while (0);
-  } else
+    if (!launched) {
+      // no cooperative launch on this device / context (MPS share, a partitioned GPU): the per-level schedule
+      // produces the same bytes
+      cudaGetLastError();
+      per_level = true;
+    }
+  }
+  if (per_level && rc != 0 && !launched)
   do {
     if (cudaMemsetAsync(src, 0, 4, s) != cudaSuccess || cudaMemsetAsync(error, 0, 4, s) != cudaSuccess) break;
     bool ok = true;
