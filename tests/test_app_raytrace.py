@@ -40,3 +40,13 @@ def test_app_fails_loudly_without_a_gpu(native, tmp_path):
     r = subprocess.run([app(native), "-o", str(tmp_path / "o.png")], capture_output=True, text=True, timeout=60)
     assert r.returncode != 0
     assert "vx_dev_open" in r.stdout
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidia0"), reason="only meaningful without a GPU")
+def test_multi_rank_app_reports_a_failed_rank_as_its_exit_code(native, tmp_path):
+    """-g 2 forks its ranks; when they cannot open a device the parent must come back with a non-zero code instead
+    of waiting for a communicator that will never form."""
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    r = subprocess.run([app(native), "-g", "2", "-o", str(tmp_path / "o.png")], capture_output=True, text=True, timeout=120, env=env)
+    assert r.returncode != 0
+    assert "vx_dev_open" in r.stdout
