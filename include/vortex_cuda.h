@@ -94,6 +94,23 @@ typedef struct {
 int vx_cuda_rt_build_lbvh(vx_device_h hdevice, vx_buffer_h soup, uint32_t num_triangles, vx_buffer_h* nodes,
                           vx_buffer_h* tris, srt_lbvh_info_t* info);
 
+/* The same build for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The caller passes the input AND both outputs: `nodes` must hold (num_triangles == 1 ? 1 :
+ * 2 x num_triangles - 1) x sizeof(srt_bvh2_node_t) bytes and `tris` num_triangles x sizeof(srt_tri_rec_t) bytes,
+ * all three distinct buffers of this device; on success they hold exactly the bytes vx_cuda_rt_build_lbvh produces
+ * for the same soup and info has the same counts.  The call allocates and frees nothing: the builder's scratch is
+ * one fixed array inside the library (5.5 MiB of device memory that every GPU which loads libvortex.so keeps until
+ * the process exits), sized for VX_CUDA_LBVH_NOALLOC_MAX_TRIS triangles.  Returns 0; -1 on bad arguments or
+ * buffers that are too small; -3, with a message on stderr, when num_triangles exceeds the maximum (use
+ * vx_cuda_rt_build_lbvh then).  Asynchronous on the launch stream.  All calls on one GPU share the array, which
+ * keeps the previous call's contents (the builder clears what it needs at zero itself): calls that can overlap on
+ * the GPU -- two vx_device handles opened on the same GPU, whose launch streams are independent -- race and must
+ * be serialised by the application (vx_ready_wait on the first before the second starts). */
+#define VX_CUDA_LBVH_NOALLOC_MAX_TRIS 65536u
+int vx_cuda_rt_build_lbvh_noalloc(vx_device_h hdevice, vx_buffer_h soup, uint32_t num_triangles, vx_buffer_h nodes,
+                                  vx_buffer_h tris, srt_lbvh_info_t* info);
+
 /* The wide-BVH image (128-byte SoA Node4 records, csrc/rt_repack.h) the last ray-tracing vx_start traversed, for
  * tests and tooling: *size = its size in bytes; copied to dst when dst != NULL and capacity suffices. */
 int vx_cuda_rt_node4_image(vx_device_h hdevice, void* dst, uint64_t capacity, uint64_t* size);

@@ -16,6 +16,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "vx_internal.h"
 
 namespace srt {
@@ -526,5 +528,162 @@ extern "C" int vx_cuda_rt_build_lbvh(vx_device_h hdevice, vx_buffer_h hsoup, uin
   info->num_tris = n;
   *hnodes = nb;
   *htris = tb;
+  return 0;
+}
+
+// ---- the same build without any allocation (include/vortex_cuda.h: vx_cuda_rt_build_lbvh_noalloc) ----------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The caller passes the
+// input AND both output buffers; the builder's scratch (sort keys, boxes, child / parent links, arrival flags) is
+// carved from one file-scope device array sized for VX_CUDA_LBVH_NOALLOC_MAX_TRIS triangles, which every GPU that
+// loads this library holds until the process exits.  All calls on one GPU share that array: it keeps the last
+// call's contents (what must start at zero is cleared below, on the stream, at every call), and two calls that
+// overlap on the GPU -- two vx_device handles of the same GPU, whose launch streams are independent -- race.
+// The launch sequence is vx_cuda_rt_build_lbvh's, restated here so that the existing entry point stays untouched.
+namespace srt {
+namespace {
+
+constexpr size_t lbvh_pad(size_t bytes) { return (bytes + 255) & ~(size_t)255; }
+constexpr size_t lbvh_scratch_bytes(size_t n, size_t npow2) {
+  return lbvh_pad(8 * sizeof(uint32_t)) + lbvh_pad(n * sizeof(uint32_t))            // scene bounds, arrival flags
+         + lbvh_pad(npow2 * sizeof(unsigned long long))                             // sort keys
+         + 2 * lbvh_pad(n * sizeof(Box)) + 2 * lbvh_pad(n * sizeof(uint2))          // leaf / node boxes, children / range
+         + 3 * lbvh_pad(n * sizeof(uint32_t));                                      // parents (2), subtree sizes
+}
+constexpr uint32_t kNoAllocMaxTris = VX_CUDA_LBVH_NOALLOC_MAX_TRIS;
+static_assert((kNoAllocMaxTris & (kNoAllocMaxTris - 1)) == 0 && kNoAllocMaxTris >= kChunk, "maximum is a padded sort size");
+constexpr size_t kNoAllocScratchBytes = lbvh_scratch_bytes(kNoAllocMaxTris, kNoAllocMaxTris);  // 5.5 MiB at 65 536
+
+}  // namespace
+}  // namespace srt
+
+// In host code this name is a host-side stand-in, not a device address: kernels get the pointer that
+// cudaGetSymbolAddress returns for the current device (noalloc_scratch below), never &g_lbvh_scratch[0].
+static __device__ __align__(256) uint8_t g_lbvh_scratch[srt::kNoAllocScratchBytes];
+
+namespace srt {
+namespace {
+
+constexpr int kMaxCudaDevices = 64;
+std::mutex g_scratch_mutex;
+uint8_t* g_scratch_ptr[kMaxCudaDevices];  // per CUDA device ordinal; filled at the first call on that device
+
+// Device address of the scratch array on `cuda_dev`, which must be the current device.
+uint8_t* noalloc_scratch(int cuda_dev) {
+  if (cuda_dev < 0 || cuda_dev >= kMaxCudaDevices) return nullptr;
+  std::lock_guard<std::mutex> lock(g_scratch_mutex);
+  if (!g_scratch_ptr[cuda_dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_lbvh_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      fprintf(stderr, "[VXDRV] vx_cuda_rt_build_lbvh_noalloc: cudaGetSymbolAddress on device %d: %s\n", cuda_dev,
+              cudaGetErrorString(e));
+      cudaGetLastError();
+      return nullptr;
+    }
+    g_scratch_ptr[cuda_dev] = static_cast<uint8_t*>(p);
+  }
+  return g_scratch_ptr[cuda_dev];
+}
+
+struct Carve {  // hands out 256-byte aligned pieces of the fixed array, in Scratch's order
+  uint8_t* base;
+  size_t used = 0;
+  explicit Carve(uint8_t* b) : base(b) {}
+  template <class T> T* take(size_t count) {
+    T* q = reinterpret_cast<T*>(base + used);
+    used += lbvh_pad((count ? count : 1) * sizeof(T));
+    return q;
+  }
+};
+
+// count = 1 for the single-leaf tree; static so that the asynchronous copy never reads a dead stack frame
+const uint32_t kOneTriangle = 1;
+
+}  // namespace
+}  // namespace srt
+
+extern "C" int vx_cuda_rt_build_lbvh_noalloc(vx_device_h hdevice, vx_buffer_h hsoup, uint32_t num_triangles,
+                                             vx_buffer_h hnodes, vx_buffer_h htris, srt_lbvh_info_t* info) {
+  if (nullptr == hdevice || nullptr == hsoup || nullptr == hnodes || nullptr == htris || nullptr == info) return -1;
+  memset(info, 0, sizeof(*info));
+  vx_device* dev = static_cast<vx_device*>(hdevice);
+  vx_buffer* sb = static_cast<vx_buffer*>(hsoup);
+  vx_buffer* nb = static_cast<vx_buffer*>(hnodes);
+  vx_buffer* tb = static_cast<vx_buffer*>(htris);
+  const uint32_t n = num_triangles;
+  if (n > kNoAllocMaxTris) {
+    fprintf(stderr, "[VXDRV] vx_cuda_rt_build_lbvh_noalloc: %u triangles exceed the fixed scratch (maximum %u = "
+                    "VX_CUDA_LBVH_NOALLOC_MAX_TRIS); use vx_cuda_rt_build_lbvh\n", n, kNoAllocMaxTris);
+    return -3;
+  }
+  const uint32_t num_nodes = n == 1 ? 1u : 2u * n - 1u;
+  if (n == 0 || sb->dev != dev || nb->dev != dev || tb->dev != dev || nb == tb || nb == sb || tb == sb ||
+      (uint64_t)n * sizeof(srt_triangle_t) > sb->size || (uint64_t)num_nodes * sizeof(srt_bvh2_node_t) > nb->size ||
+      (uint64_t)n * sizeof(srt_tri_rec_t) > tb->size) {
+    fprintf(stderr, "[VXDRV] vx_cuda_rt_build_lbvh_noalloc: bad arguments (%u triangles need %llu node bytes and "
+                    "%llu record bytes in buffers of this device)\n", n,
+            (unsigned long long)num_nodes * sizeof(srt_bvh2_node_t), (unsigned long long)n * sizeof(srt_tri_rec_t));
+    return -1;
+  }
+  VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
+  uint8_t* scratch = noalloc_scratch(dev->cuda_dev);
+  if (!scratch) return -1;
+  cudaStream_t s = dev->stream;
+  const srt_triangle_t* soup = static_cast<const srt_triangle_t*>(sb->dptr);
+  srt_bvh2_node_t* nodes = static_cast<srt_bvh2_node_t*>(nb->dptr);
+  float4* recs = static_cast<float4*>(tb->dptr);
+  uint32_t npow2 = kChunk;
+  while (npow2 < n) npow2 <<= 1;
+
+  Carve tmp(scratch);
+  uint32_t* scene = tmp.take<uint32_t>(8);
+  uint32_t* arrived = tmp.take<uint32_t>(n);
+  const size_t head = tmp.used;  // scene bounds + arrival flags: cleared at every call
+  unsigned long long* keys = tmp.take<unsigned long long>(npow2);
+  Box* leaf_box = tmp.take<Box>(n);
+  Box* node_box = tmp.take<Box>(n);
+  uint2* children = tmp.take<uint2>(n);
+  uint2* range = tmp.take<uint2>(n);
+  uint32_t* parent_internal = tmp.take<uint32_t>(n);
+  uint32_t* parent_leaf = tmp.take<uint32_t>(n);
+  uint32_t* count = tmp.take<uint32_t>(n);
+  if (tmp.used > kNoAllocScratchBytes) return -1;  // cannot happen for n <= the maximum (lbvh_scratch_bytes)
+  const uint32_t rot_dcr = vx_dev_dcr(dev, VX_DCR_RT_LBVH_ROTATE);
+  const uint32_t rotate_passes = rot_dcr == 0 ? 2u : (rot_dcr - 1u > 8u ? 8u : rot_dcr - 1u);
+  int rc = -1;
+  do {
+    if (cudaMemsetAsync(scratch, 0, head, s) != cudaSuccess) break;
+    if (cudaMemsetAsync(scene, 0xff, 3 * sizeof(uint32_t), s) != cudaSuccess) break;
+    if (cudaMemsetAsync(nodes, 0, (size_t)num_nodes * sizeof(srt_bvh2_node_t), s) != cudaSuccess) break;
+    const uint32_t blocks = (n + 255) / 256;
+    lbvh_bounds_kernel<<<blocks < 1184 ? blocks : 1184, 256, 0, s>>>(soup, n, scene);
+    lbvh_keys_kernel<<<(npow2 + 255) / 256, 256, 0, s>>>(soup, n, npow2, scene, keys);
+    if (sort_keys(s, keys, npow2) != 0) break;
+    lbvh_leaves_kernel<<<blocks, 256, 0, s>>>(soup, n, keys, recs, leaf_box);
+    if (n == 1) {
+      if (cudaMemcpyAsync(&nodes[0].bmin, &leaf_box[0].lo, 12, cudaMemcpyDeviceToDevice, s) != cudaSuccess) break;
+      if (cudaMemcpyAsync(&nodes[0].bmax, &leaf_box[0].hi, 12, cudaMemcpyDeviceToDevice, s) != cudaSuccess) break;
+      if (cudaMemcpyAsync(&nodes[0].count, &kOneTriangle, 4, cudaMemcpyHostToDevice, s) != cudaSuccess) break;
+    } else {
+      lbvh_hierarchy_kernel<<<blocks, 256, 0, s>>>(keys, n, children, range, parent_internal, parent_leaf, count);
+      lbvh_refit_kernel<<<blocks, 256, 0, s>>>(n, children, parent_internal, parent_leaf, leaf_box, node_box, arrived);
+      bool ok = true;
+      for (uint32_t pass = 0; pass < rotate_passes && ok; ++pass) {
+        ok = cudaMemsetAsync(arrived, 0, (size_t)n * sizeof(uint32_t), s) == cudaSuccess;
+        lbvh_rotate_kernel<<<blocks, 256, 0, s>>>(n, children, parent_internal, parent_leaf, leaf_box, node_box, count, arrived);
+      }
+      if (!ok) break;
+      lbvh_emit_kernel<<<blocks, 256, 0, s>>>(n, children, range, count, leaf_box, node_box, nodes);
+    }
+    if (cudaGetLastError() != cudaSuccess) break;
+    rc = 0;
+  } while (0);
+  if (rc != 0) {
+    fprintf(stderr, "[VXDRV] lbvh build (no allocation) failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+    return -1;
+  }
+  info->num_nodes = num_nodes;
+  info->num_tris = n;
   return 0;
 }

@@ -104,6 +104,18 @@ def make_arg(width, height, mode, spp=1, seed=1234, scene="cornell", rank=0, num
     return a
 
 
+def build_lbvh_noalloc(dev, soup_buf, num_triangles, node_buf, tri_buf):
+    """vx_cuda_rt_build_lbvh_noalloc (include/vortex_cuda.h): the device BVH build into buffers the caller owns, with
+    the builder's scratch in a fixed array inside libvortex.so -- no allocation in the call.  No counterpart in the
+    reference.  Returns (num_nodes, num_tris); raises VortexError (code -3 above VX_CUDA_LBVH_NOALLOC_MAX_TRIS)."""
+    info = (C.c_uint32 * 2)()
+    rc = vx.lib().vx_cuda_rt_build_lbvh_noalloc(dev.handle, soup_buf.handle, num_triangles, node_buf.handle,
+                                                tri_buf.handle, info)
+    if rc != 0:
+        raise vx.VortexError(f"vx_cuda_rt_build_lbvh_noalloc failed with code {rc}")
+    return info[0], info[1]
+
+
 class RayTracer:
     """One opened device with one uploaded scene."""
 

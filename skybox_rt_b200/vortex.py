@@ -55,7 +55,9 @@ CUDA_EXPORTS = ["vx_cuda_stream", "vx_cuda_device", "vx_cuda_host_register", "vx
                 "vx_cuda_perf_totals", "vx_cuda_draw3d_binning", "vx_cuda_rt_build_lbvh",
                 "vx_cuda_rt_node4_image", "vx_cuda_fill32", "vx_cuda_probe_read_bandwidth",
                 "vx_cuda_comm_unique_id", "vx_cuda_comm_init", "vx_cuda_comm_destroy", "vx_cuda_frame_gather",
-                "vx_cuda_gather_bytes", "vx_cuda_frame_gather_inplace", "vx_cuda_copy_from_dev_async", "vx_cuda_copy_wait"]  # include/vortex_cuda.h
+                "vx_cuda_gather_bytes", "vx_cuda_frame_gather_inplace", "vx_cuda_copy_from_dev_async", "vx_cuda_copy_wait",
+                "vx_cuda_rt_build_lbvh_noalloc"]  # include/vortex_cuda.h
+VX_CUDA_LBVH_NOALLOC_MAX_TRIS = 65536
 VX_CUDA_COMM_ID_BYTES = 128
 
 _lib = None
@@ -94,6 +96,7 @@ def lib():
             "vx_cuda_stream": [vp, C.POINTER(vp)], "vx_cuda_device": [vp, C.POINTER(i)],
             "vx_cuda_perf_totals": [vp, C.POINTER(u64), u32],
             "vx_cuda_rt_build_lbvh": [vp, vp, u32, C.POINTER(vp), C.POINTER(vp), vp],
+            "vx_cuda_rt_build_lbvh_noalloc": [vp, vp, u32, vp, vp, vp],
             "vx_cuda_rt_node4_image": [vp, vp, u64, C.POINTER(u64)],
             "vx_cuda_fill32": [vp, u64, u64, u32],
             "vx_cuda_probe_read_bandwidth": [vp, u64, u32, C.POINTER(C.c_float)],
