@@ -246,6 +246,9 @@ typedef struct {
 #define VX_DCR_RASTER_EXT_TBUF_FORMAT 0x804 /* back-end DCR (outside the reference's ranges); 0 after open */
 #define VX_DCR_RASTER_EXT_GENERIC 0x805     /* 1 = never use the state-specialised kernels (A/B testing)   */
 #define VX_DCR_RASTER_EXT_PPT 0x806         /* pixels per thread: 0 = by grid size, 4 = quad, 1 = pixel    */
+#define VX_DCR_RASTER_EXT_TILE_LOGSIZE 0x80D /* log2 tile size the app binned its tile buffers with, 0 = undeclared:
+                                                vx_start refuses any other value than RASTER_TILE_LOGSIZE, because the
+                                                kernel is built for that size and the buffer formats do not carry it */
 
 typedef struct {
   uint8_t* tilebuf;   uint64_t tilebuf_size;

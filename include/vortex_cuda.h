@@ -67,8 +67,10 @@ int vx_cuda_perf_totals(vx_device_h hdevice, uint64_t* out, uint32_t count);
  * once for the output sizes.
  * tile_logsize: buffers handed to vx_start must be binned with RASTER_TILE_LOGSIZE (5, 32x32 pixels): the render
  * kernel is built for that size like the reference's raster unit (hw/rtl/VX_config.vh:477-478) and neither tile
- * buffer format carries the size, so a buffer binned otherwise cannot be told apart and renders wrongly.  Other
- * sizes (1..8) exist for tooling and for the byte-for-byte comparison with graphics::Binning at its other sizes. */
+ * buffer format carries the size.  The tile buffer returned here remembers its size and vx_start refuses it (-1, with
+ * a message) when it is not 5; for tile buffers binned on the host and uploaded, the app can declare the size in
+ * VX_DCR_RASTER_EXT_TILE_LOGSIZE (include/skybox_draw3d.h) for the same check.  Other sizes (1..8) exist for tooling
+ * and for the byte-for-byte comparison with graphics::Binning at its other sizes. */
 typedef struct {
   uint32_t num_tiles, num_prims;
   uint64_t num_tile_prims; /* sum of pids_count */

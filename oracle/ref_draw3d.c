@@ -1076,3 +1076,49 @@ int ref_draw3d_depth_stencil(const draw3d_kernel_arg_t* arg, uint32_t depth, uin
 uint32_t ref_draw3d_tex(const draw3d_kernel_arg_t* arg, const uint8_t* texels, int32_t u, int32_t v) {
   return tex_read(arg, texels, u, v, 0);
 }
+
+/* The reference's texture-unit regression kernel (tests/regression/tex/kernel.cpp:42-134) over the texture state of
+ * stage 0 in `arg`: a dst_width x dst_height image whose pixel (x, y) samples the texture at ((x + 0.5) / W,
+ * (y + 0.5) / H), the coordinates accumulated in fp32 task by task exactly as the kernel does (fu += deltaX), at the
+ * mip level its main() derives from the minification.  `trilinear` is the kernel's `filter == 2` branch (two levels
+ * blended by `frac`; the reference app never sets that field, tex/main.cpp:231-252).  out: row 0 first. */
+void ref_draw3d_tex_image(const draw3d_kernel_arg_t* arg, const uint8_t* texels, uint32_t dst_width, uint32_t dst_height,
+                          uint32_t num_tasks, int trilinear, uint32_t* out) {
+  if (num_tasks == 0) num_tasks = 1;
+  if (num_tasks > dst_height) num_tasks = dst_height; /* tex/main.cpp:235 */
+  /* kernel.cpp:106-128 main() */
+  const uint32_t tile_height = (dst_height + num_tasks - 1) / num_tasks;
+  const float deltaX = 1.0f / dst_width, deltaY = 1.0f / dst_height;
+  const uint32_t logdim = TEX(arg, VX_DCR_TEX_LOGDIM);
+  const float width_ratio = (float)(1 << (logdim & 0xffff)) / dst_width;
+  const float height_ratio = (float)(1 << (logdim >> 16)) / dst_height;
+  float minification = width_ratio > height_ratio ? width_ratio : height_ratio;
+  if (minification < 1.0f) minification = 1.0f;
+  const int32_t j = (int32_t)(minification * 65536); /* fixed16_t(float): fixed.hpp:97-100 */
+  uint32_t lod = (uint32_t)(31 - __builtin_clz((uint32_t)j)) - 16;
+  if (lod > VX_TEX_LOD_MAX) lod = VX_TEX_LOD_MAX;
+  const uint32_t frac = (uint32_t)(j - (1 << (lod + 16))) >> (lod + 16 - 8);
+  const uint32_t lodn = lod + 1 < VX_TEX_LOD_MAX ? lod + 1 : VX_TEX_LOD_MAX;
+  /* kernel.cpp:42-103 kernel_body, one call per task */
+  for (uint32_t task = 0; task < num_tasks; ++task) {
+    const uint32_t y_start = task * tile_height;
+    const uint32_t y_end = y_start + tile_height < dst_height ? y_start + tile_height : dst_height;
+    float fv = (y_start + 0.5f) * deltaY;
+    for (uint32_t y = y_start; y < y_end; ++y) {
+      float fu = (0 + 0.5f) * deltaX;
+      for (uint32_t x = 0; x < dst_width; ++x) {
+        const int32_t xu = (int32_t)(fu * (1 << VX_TEX_FXD_FRAC)), xv = (int32_t)(fv * (1 << VX_TEX_FXD_FRAC));
+        uint32_t color = tex_read(arg, texels, xu, xv, lod);
+        if (trilinear) {
+          const uint32_t texel1 = tex_read(arg, texels, xu, xv, lodn);
+          const uint32_t cl = lerp8888(color & 0x00ff00ff, texel1 & 0x00ff00ff, frac);
+          const uint32_t ch = lerp8888((color >> 8) & 0x00ff00ff, (texel1 >> 8) & 0x00ff00ff, frac);
+          color = (ch << 8) | cl;
+        }
+        out[(uint64_t)y * dst_width + x] = color;
+        fu += deltaX;
+      }
+      fv += deltaY;
+    }
+  }
+}

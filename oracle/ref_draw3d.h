@@ -50,6 +50,9 @@ uint32_t ref_draw3d_prim_size(void);
 uint32_t ref_draw3d_blend(const draw3d_kernel_arg_t* arg, uint32_t src, uint32_t dst);
 int ref_draw3d_depth_stencil(const draw3d_kernel_arg_t* arg, uint32_t depth, uint32_t dst_ds, uint32_t* out_ds);
 uint32_t ref_draw3d_tex(const draw3d_kernel_arg_t* arg, const uint8_t* texels, int32_t u, int32_t v);
+/* tests/regression/tex/kernel.cpp restated: the texture of stage 0 resampled to dst_width x dst_height. */
+void ref_draw3d_tex_image(const draw3d_kernel_arg_t* arg, const uint8_t* texels, uint32_t dst_width, uint32_t dst_height,
+                          uint32_t num_tasks, int trilinear, uint32_t* out);
 
 #ifdef __cplusplus
 }

@@ -225,7 +225,8 @@ int srt_draw3d_open(vx_device_h device, uint32_t width, uint32_t height, uint32_
       vx_mem_alloc(device, r->cbuf_size, VX_MEM_READ_WRITE, &r->color_buffer) != 0 ||
       vx_mem_address(r->color_buffer, &r->cbuf_addr) != 0 ||
       vx_dcr_write(device, VX_DCR_RASTER_EXT_TBUF_FORMAT,
-                   (flags & SRT_DRAW3D_WIDE_TILES) ? SRT_TILEBUF_WIDE : SRT_TILEBUF_REFERENCE) != 0) {
+                   (flags & SRT_DRAW3D_WIDE_TILES) ? SRT_TILEBUF_WIDE : SRT_TILEBUF_REFERENCE) != 0 ||
+      vx_dcr_write(device, VX_DCR_RASTER_EXT_TILE_LOGSIZE, RASTER_TILE_LOGSIZE) != 0) {
     srt_draw3d_close(r);
     return -1;
   }

@@ -454,6 +454,7 @@ extern "C" int vx_cuda_draw3d_binning(vx_device_h hdevice, vx_buffer_h hvertices
       }
     }
   }
+  if (tb) static_cast<vx_buffer*>(tb)->tile_logsize = tile_logsize;  // raster_launch refuses sizes its kernel is not built for
   *htilebuf = tb;
   *hprimbuf = prb;
   return 0;

@@ -29,12 +29,17 @@ enum { RCTR_FRAGMENTS = 0, RCTR_TESTS, RCTR_TEXELS, RCTR_OM_READS, RCTR_OM_WRITE
 struct RasterState {
   unsigned long long* d_counters = nullptr;  // RCTR_COUNT u64
   bool counters_live = false;                // the last launch counted
+  // RASTER_FAULT_* bits set by a tile kernel that met a primitive list or id outside its buffer: one page-locked,
+  // device-mapped word, read by the host once the stream is idle (raster_take_fault)
+  volatile uint32_t* h_fault = nullptr;
+  uint32_t* d_fault = nullptr;
 };
 
 namespace {
 
 // Finds the allocation whose 64-byte block address matches `block` in its low 32 bits.
-uint8_t* resolve_block(vx_device* dev, uint32_t block, const char* what, uint64_t* size_left) {
+uint8_t* resolve_block(vx_device* dev, uint32_t block, const char* what, uint64_t* size_left,
+                       const vx_buffer** owner = nullptr) {
   uint8_t* found = nullptr;
   int matches = 0;
   for (vx_buffer* b = dev->buffers; b; b = b->next) {
@@ -45,6 +50,7 @@ uint8_t* resolve_block(vx_device* dev, uint32_t block, const char* what, uint64_
     if (cand >= lo && cand < hi) {
       found = (uint8_t*)b->dptr + (cand - lo);
       if (size_left) *size_left = hi - cand;
+      if (owner) *owner = b;
       ++matches;
     }
   }
@@ -97,9 +103,37 @@ int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg) {
     return -1;
   }
   uint64_t tb_left = 0, pb_left = 0;
-  P.tilebuf = resolve_block(dev, ras(VX_DCR_RASTER_TBUF_ADDR), "tile buffer", &tb_left);
+  const vx_buffer* tb_owner = nullptr;
+  P.tilebuf = resolve_block(dev, ras(VX_DCR_RASTER_TBUF_ADDR), "tile buffer", &tb_left, &tb_owner);
   P.primbuf = resolve_block(dev, ras(VX_DCR_RASTER_PBUF_ADDR), "primitive buffer", &pb_left);
   if (!P.tilebuf || !P.primbuf) return -1;
+  // The kernel is built for 32 x 32-pixel tiles (RASTER_TILE_LOGSIZE, like the reference's raster unit) and neither
+  // tile-buffer format carries the size it was binned with.  What is known is checked: the size vx_cuda_draw3d_binning
+  // recorded on the buffer it returned, else the size the app declared in VX_DCR_RASTER_EXT_TILE_LOGSIZE (0 = undeclared).
+  const uint32_t binned = tb_owner->tile_logsize ? tb_owner->tile_logsize : dev_dcr(dev, VX_DCR_RASTER_EXT_TILE_LOGSIZE);
+  if (binned != 0 && binned != RASTER_TILE_LOGSIZE) {
+    fprintf(stderr, "[VXDRV] draw3d: the tile buffer was binned with 2^%u-pixel tiles; this back-end renders 2^%u only\n",
+            binned, (unsigned)RASTER_TILE_LOGSIZE);
+    return -1;
+  }
+  P.tilebuf_bytes = tb_left;
+  P.prim_limit = (uint32_t)(pb_left / P.prim_stride > 0xffffffffull ? 0xffffffffull : pb_left / P.prim_stride);
+  if (P.prim_limit == 0) {
+    fprintf(stderr, "[VXDRV] draw3d: the primitive buffer holds no whole record of %u bytes\n", P.prim_stride);
+    return -1;
+  }
+  if (!st->h_fault) {
+    uint32_t* h = nullptr;
+    VX_CUDA_OK(cudaHostAlloc((void**)&h, sizeof(uint32_t), cudaHostAllocMapped));
+    *h = 0;
+    if (cudaHostGetDevicePointer((void**)&st->d_fault, h, 0) != cudaSuccess) {
+      cudaFreeHost(h);
+      cudaGetLastError();
+      return -1;
+    }
+    st->h_fault = h;
+  }
+  P.fault = st->d_fault;
   const uint64_t hdr = P.tile_format == SRT_TILEBUF_WIDE ? sizeof(srt_tile_header_wide_t) : sizeof(rast_tile_header_t);
   if ((uint64_t)P.num_tiles * hdr > tb_left) {
     fprintf(stderr, "[VXDRV] draw3d: %u tile headers do not fit the tile buffer\n", P.num_tiles);
@@ -265,8 +299,21 @@ int raster_read_counters(vx_device* dev) {
   return 0;
 }
 
+// Called when the launch stream has drained: reports and clears what the tile kernels flagged since the last call.
+int raster_take_fault(vx_device* dev) {
+  RasterState* st = dev->raster;
+  if (!st || !st->h_fault) return 0;
+  const uint32_t bits = *st->h_fault;
+  if (bits == 0) return 0;
+  *st->h_fault = 0;
+  if (bits & RASTER_FAULT_LIST) fprintf(stderr, "[VXDRV] draw3d: a tile's primitive list lies outside the tile buffer (tile skipped)\n");
+  if (bits & RASTER_FAULT_PRIM) fprintf(stderr, "[VXDRV] draw3d: a primitive id lies outside the primitive buffer (record 0 drawn instead)\n");
+  return -1;
+}
+
 void raster_destroy(vx_device* dev) {
   if (!dev->raster) return;
+  if (dev->raster->h_fault) cudaFreeHost(const_cast<uint32_t*>(dev->raster->h_fault));
   cudaFree(dev->raster->d_counters);
   delete dev->raster;
   dev->raster = nullptr;

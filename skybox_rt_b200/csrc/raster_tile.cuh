@@ -37,6 +37,9 @@ struct RasterParams {
   const uint8_t* tilebuf;
   const uint8_t* primbuf;
   uint32_t num_tiles, tile_format, prim_stride;
+  uint32_t prim_limit;      // whole primitive records the primitive buffer holds: a larger id is refused
+  uint64_t tilebuf_bytes;   // bytes of the tile buffer from `tilebuf` on: a primitive list that leaves them is refused
+  uint32_t* fault;          // device view of the page-locked fault word the host reads after the run (RASTER_FAULT_*)
   uint32_t scissor_left, scissor_right, scissor_top, scissor_bottom;
   // output merger
   uint8_t* cbuf;
@@ -55,6 +58,7 @@ struct RasterParams {
   unsigned long long* counters;                      // RCTR_* slots of raster_pipeline.cu (STATS instantiations only)
 };
 
+enum { RASTER_FAULT_LIST = 1, RASTER_FAULT_PRIM = 2 };  // bits of *RasterParams::fault
 constexpr int kRasterThreads = 256;
 constexpr int kPrimChunk = 48;  // primitives staged per round: 48 * 120 B = 5760 B of shared memory
 
@@ -355,6 +359,11 @@ __global__ void __launch_bounds__(PPT == 4 ? kRasterThreads : 1024) raster_tile_
     tile_x = hv.x & 0xffff; tile_y = hv.x >> 16; pids_count = hv.y >> 16;
     pids = reinterpret_cast<const uint32_t*>(h + 1) + (hv.y & 0xffff);
   }
+  // a malformed tile buffer must not become a device fault: a list that leaves the buffer is skipped and reported
+  if ((uint64_t)(reinterpret_cast<const uint8_t*>(pids) - P.tilebuf) + 4ull * pids_count > P.tilebuf_bytes) {
+    if (tid == 0) atomicOr(P.fault, (uint32_t)RASTER_FAULT_LIST);
+    pids_count = 0;
+  }
   const uint32_t X0 = tile_x << RASTER_TILE_LOGSIZE, Y0 = tile_y << RASTER_TILE_LOGSIZE;
   // PPT 4: warp = 16x8 pixels (8x4 quads); PPT 1: warp = 8x4 pixels.  Either way inside one 16x16 block.
   const uint32_t lx = PPT == 4 ? ((warp & 1) << 4) + ((lane & 7) << 1) : ((warp & 3) << 3) + (lane & 7);
@@ -394,7 +403,11 @@ __global__ void __launch_bounds__(PPT == 4 ? kRasterThreads : 1024) raster_tile_
     __syncthreads();  // previous chunk fully consumed
     for (uint32_t w = tid; w < n * 30; w += NT) {
       const uint32_t k = w / 30, j = w - k * 30;
-      const uint32_t pid = __ldg(pids + base + k);
+      uint32_t pid = __ldg(pids + base + k);
+      if (pid >= P.prim_limit) {  // an id past the primitive buffer: record 0 stands in and the run is reported
+        if (j == 0) atomicOr(P.fault, (uint32_t)RASTER_FAULT_PRIM);
+        pid = 0;
+      }
       s_prims[k][j] = __ldg(reinterpret_cast<const int32_t*>(P.primbuf + (size_t)pid * P.prim_stride) + j);
     }
     __syncthreads();

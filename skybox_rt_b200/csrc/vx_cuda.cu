@@ -300,7 +300,7 @@ int vx_copy_from_dev(void* host_ptr, vx_buffer_h hbuffer, uint64_t src_offset, u
   VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
   VX_CUDA_OK(cudaMemcpyAsync(host_ptr, (const char*)b->dptr + src_offset, size, cudaMemcpyDeviceToHost, dev->stream));
   VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
-  return 0;
+  return srt::raster_take_fault(dev);  // what is read back may come from a draw that met a malformed tile buffer
 }
 
 // ------------------------------------------------------------------------------- execution
@@ -421,7 +421,7 @@ int vx_ready_wait(vx_device_h hdevice, uint64_t timeout) {
   clock_gettime(CLOCK_MONOTONIC, &t0);
   for (uint64_t spins = 0;; ++spins) {
     cudaError_t e = cudaStreamQuery(dev->stream);
-    if (e == cudaSuccess) return 0;
+    if (e == cudaSuccess) return srt::raster_take_fault(dev);
     if (e != cudaErrorNotReady) {
       fprintf(stderr, "[VXDRV] device fault: %s\n", cudaGetErrorString(e));
       return -1;

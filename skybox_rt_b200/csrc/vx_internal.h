@@ -27,6 +27,7 @@ struct vx_buffer {
   uint8_t* shadow;        // host copy of small host-written buffers (kernel args, kernel images)
   uint64_t generation;    // bumped by every vx_copy_to_dev (invalidates derived device data)
   uint64_t uid;           // device-wide allocation number, never reused (the pool does reuse addresses)
+  uint32_t tile_logsize;  // tile buffers made by vx_cuda_draw3d_binning: the tile size they were binned with, else 0
   vx_buffer* prev;
   vx_buffer* next;
 };
@@ -144,6 +145,7 @@ void rt_buffer_freed(vx_device* dev, const vx_buffer* b);  // drops derived data
 // raster_pipeline.cu
 int raster_launch(vx_device* dev, const draw3d_kernel_arg_t& arg);
 int raster_read_counters(vx_device* dev);
+int raster_take_fault(vx_device* dev);  // -1 (+ a message) when a tile kernel met data outside its buffers since the last call
 void raster_destroy(vx_device* dev);
 }  // namespace srt
 

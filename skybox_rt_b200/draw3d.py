@@ -22,6 +22,7 @@ AUTO = 64  # device clear / device binning where they pay, no wait between the d
 TILEBUF_REFERENCE, TILEBUF_WIDE = 0, 1
 VX_CSR_RASTER_FRAGMENTS, VX_CSR_RASTER_QUAD_TESTS, VX_CSR_RASTER_TILES = 0x7C8, 0x7C9, 0x7CA
 VX_DCR_RASTER_EXT_TBUF_FORMAT = 0x804
+VX_DCR_RASTER_EXT_TILE_LOGSIZE = 0x80D  # tile size the buffers were binned with; vx_start refuses anything but 5
 
 
 class Binning(C.Structure):  # srt_binning_t (include/skybox_draw3d.h)

@@ -206,3 +206,114 @@ def om_override_variants():
         v.append((f"dst factor={f}", (ADD << 16 | ADD, func(SRC_A, SRC_A, f, f), cst, 0)))
         v.append((f"factor={f} REV_SUB", (REV_SUB << 16 | REV_SUB, func(f, ONE, ONE, f), 0xFF102030, 0)))
     return v
+
+
+# ---- the reference's sub-unit regression apps (tests/regression/{tex,raster,om}); fixtures from
+# tests/golden/make_unit_fixtures.py ------------------------------------------------------------------------------
+UNITS_DIR = os.path.join(ROOT, "tests", "golden", "units")
+TEX_DCRS_OFFSET = 24  # draw3d_kernel_arg_t.tex_dcrs (include/skybox_draw3d.h), stage 0 first
+TEX_ADDR, TEX_LOGDIM, TEX_FORMAT, TEX_FILTER, TEX_WRAP, TEX_MIPOFF0 = 0, 1, 2, 3, 4, 5  # index = DCR - TEX_STATE_BEGIN - 1
+
+
+def unit_fixtures(unit):
+    return np.load(os.path.join(UNITS_DIR, unit + ".npz"))
+
+
+def tex_kernel_arg(fmt, width, height, wrap, filt, mips):
+    """A draw3d kernel_arg_t image whose stage-0 texture state is what tests/regression/tex/main.cpp:243-252 programs."""
+    arg = np.zeros(oracle().ref_draw3d_kernel_arg_size() // 4, np.uint32)
+    t = arg[TEX_DCRS_OFFSET // 4:]
+    t[TEX_LOGDIM] = ((int(height).bit_length() - 1) << 16) | (int(width).bit_length() - 1)
+    t[TEX_FORMAT] = fmt
+    t[TEX_WRAP] = (wrap << 16) | wrap
+    t[TEX_FILTER] = 1 if filt else 0
+    for i, off in enumerate(mips):
+        t[TEX_MIPOFF0 + i] = off
+    return arg
+
+
+def tex_image(arg, chain, dst_width, dst_height, tasks, trilinear=0):
+    """oracle/ref_draw3d.c: ref_draw3d_tex_image, the restatement of tests/regression/tex/kernel.cpp."""
+    L = oracle()
+    L.ref_draw3d_tex_image.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
+    L.ref_draw3d_tex_image.restype = None
+    chain = np.ascontiguousarray(chain, np.uint8)
+    out = np.zeros((dst_height, dst_width), np.uint32)
+    L.ref_draw3d_tex_image(arg.ctypes.data, chain.ctypes.data, dst_width, dst_height, tasks, trilinear, out.ctypes.data)
+    return out
+
+
+def reference_tex():
+    """oracle/_ref/libref_tex.so (the reference's own texture app, oracle/ref_tex_harness.cpp), or None."""
+    if "ref_tex" not in _libs:
+        _make()
+        p = os.path.join(ORACLE_DIR, "_ref", "libref_tex.so")
+        L = None
+        if os.path.exists(p):
+            L = C.CDLL(p)
+            L.ref_tex_render.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p] + [C.c_uint32] * 9 + [C.c_void_p]
+        _libs["ref_tex"] = L
+    return _libs["ref_tex"]
+
+VX_OM_DEPTH_FUNC_ALWAYS = 0  # include/skybox_draw3d.h:73
+OM_DCRS_OFFSET = 196  # draw3d_kernel_arg_t.om_dcrs; index = DCR - VX_DCR_OM_STATE_BEGIN
+(OM_CBUF_ADDR, OM_CBUF_PITCH, OM_CBUF_WRITEMASK, OM_ZBUF_ADDR, OM_ZBUF_PITCH, OM_DEPTH_FUNC, OM_DEPTH_WRITEMASK,
+ OM_STENCIL_FUNC, OM_STENCIL_ZPASS, OM_STENCIL_ZFAIL, OM_STENCIL_FAIL, OM_STENCIL_REF, OM_STENCIL_MASK,
+ OM_STENCIL_WRITEMASK, OM_BLEND_MODE, OM_BLEND_FUNC, OM_BLEND_CONST, OM_LOGIC_OP) = range(18)
+
+TEX_TO_COCOGFX = {0: 5, 1: 4, 2: 6, 3: 8, 4: 3, 5: 2, 6: 1}  # VX_TEX_FORMAT_* -> cocogfx ePixelFormat (format.hpp:24-37)
+TEX_BPP = {0: 4, 1: 2, 2: 2, 3: 2, 4: 2, 5: 1, 6: 1}
+
+
+def quad_trace(width, height, texture=None, bilinear=False, repeat=False, color=(1.0, 1.0, 1.0, 1.0)):
+    """One draw call (SKBXTRC1, tests/golden/make_raster_fixtures.py) of two triangles that cover the whole
+    width x height viewport, texture coordinates (0, 0) at framebuffer pixel (0, 0): with a texture
+    (= (VX_TEX_FORMAT, texel bytes of level 0, w, h)) and texture environment REPLACE every fragment (x, y) samples at
+    ((x + 0.5) / width, (y + 0.5) / height) -- the image tests/regression/tex renders, here through binning, raster,
+    attribute interpolation, sampler, texenv and output merger; without one the fragments carry the vertex colour
+    (tests/regression/om's constant-colour box)."""
+    import struct
+    out = b"SKBXTRC1" + struct.pack("<II", 1, 1 if texture else 0)
+    if texture:
+        fmt, pix, w, h = texture
+        pix = bytes(pix)
+        out += struct.pack("<5I", 1, TEX_TO_COCOGFX[fmt], w, h, len(pix)) + pix + b"\0" * (-len(pix) % 4)
+    filt = 2 if bilinear else 1   # SRT_FILTER_LINEAR / NEAREST
+    addr = 0 if repeat else 1     # SRT_ADDRESS_WRAP / CLAMP
+    states = [0 if texture else 1, 5, 0xF] + [0] * 12 + [1 if texture else 0, 2, filt, filt, addr, addr, 0, 0, 0]
+    out += struct.pack("<24I", *states) + struct.pack("<4f", 0, 0, 0, 0) + struct.pack("<I", 1 if texture else 0)
+    out += struct.pack("<4i2f", 0, width, 0, height, 0.0, 1.0)
+    out += struct.pack("<II", 4, 2)
+    for x, y, u, v in ((-1, -1, 0, 0), (1, -1, 1, 0), (-1, 1, 0, 1), (1, 1, 1, 1)):
+        out += struct.pack("<10f", x, y, 0, 1, *color, u, v)
+    return out + struct.pack("<6I", 0, 1, 2, 2, 1, 3)
+
+
+def tex_unit_cases():
+    """[(id, trace blob, w, h, expected image or None)] for the texture fixtures: the 19 golden PNGs and every
+    reference-rendered vector of level 0 whose coordinates the raster path reproduces exactly (power-of-two sizes;
+    clamp / repeat -- a trace cannot ask for mirror); the other level-0 vectors come with expected = None (the path
+    computes their coordinates differently: compare with the oracle's frame instead)."""
+    T = unit_fixtures("tex")
+
+    def tex_of(name, fmt):
+        w, h = (int(x) for x in T[f"tex/{name}/f{fmt}/dim"])
+        return fmt, T[f"tex/{name}/f{fmt}"][:w * h * TEX_BPP[fmt]].tobytes(), w, h
+
+    cases = []
+    for f in range(7):
+        cases.append((f"toad_ref_f{f}", quad_trace(64, 64, tex_of("toad", f)), 64, 64, T[f"golden/toad_ref_f{f}"]))
+    for name in ("soccer", "palette4", "palette16", "palette64"):
+        for g in range(3):
+            t = tex_of(name, 0)
+            cases.append((f"{name}_ref_g{g}", quad_trace(t[2], t[3], t, bilinear=g > 0), t[2], t[3], T[f"golden/{name}_ref_g{g}"]))
+    for key in sorted(k for k in T.files if k.startswith("run/")):
+        m = re.match(r"run/(\w+)/f(\d)/w(\d)/g(\d)/(\d+)x(\d+)/t(\d+)$", key)
+        name, (fmt, wrap, filt, dw, dh, _) = m.group(1), (int(x) for x in m.groups()[1:])
+        t = tex_of(name, fmt)
+        if wrap == 2 or dw < t[2] or dh < t[3]:
+            continue
+        exact = (dw & (dw - 1)) == 0 and (dh & (dh - 1)) == 0
+        cases.append((key[4:].replace("/", "-"), quad_trace(dw, dh, t, bilinear=bool(filt), repeat=bool(wrap)), dw, dh,
+                      T[key] if exact else None))
+    return cases

@@ -304,3 +304,119 @@ def test_device_fill_and_device_clear(d3):
         for _ in range(2):  # the second frame starts from a dirty target
             got_c, got_z = app.frame(t), app.read(depth=True)
     assert np.array_equal(got_c, want_c) and np.array_equal(got_z, want_z)
+
+
+class RawDraw:
+    """One draw of the triangle trace driven through the raw vx_* calls (the flow of the test above), with the tile and
+    primitive buffers supplied by the caller -- for the checks vx_start and the tile kernel make on them."""
+
+    def __init__(self, d3, native, size=64):
+        import ctypes as C
+
+        from skybox_rt_b200 import vortex as vx
+        self.vx, self.size = vx, size
+        self.trace = d3.Trace(blob=od.trace_blob("triangle"))
+        self.dev = vx.Device()
+        k = C.c_void_p()
+        path = os.path.join(os.path.dirname(native["vortex"]), "draw3d.vxbin").encode()
+        assert vx.lib().vx_upload_kernel_file(self.dev.handle, path, C.byref(k)) == 0
+        self.kernel = vx.Buffer(self.dev, k, 32)
+        self.cbuf = self.dev.alloc(size * size * 4)
+
+    def draw(self, n, tile, prim):
+        """tile / prim: device buffers.  Raises VortexError where vx_start or vx_ready_wait report a failure."""
+        vx, dev, W = self.vx, self.dev, self.size
+        self.cbuf.write(np.full(W * W, 0xFF000000, np.uint32))
+        arg = np.zeros(288 // 4, np.uint32)
+        arg[268 // 4] = 6
+        arg[272 // 4], arg[276 // 4] = prim.address & 0xFFFFFFFF, prim.address >> 32
+        arg.view(np.uint8)[281] = 1
+        RAS, OM = 28, 34
+        for a, v in [(RAS + 0, (tile.address // 64) & 0xFFFFFFFF), (RAS + 1, n), (RAS + 2, (prim.address // 64) & 0xFFFFFFFF),
+                     (RAS + 3, 120), (RAS + 4, W << 16), (RAS + 5, W << 16), (OM + 0, (self.cbuf.address // 64) & 0xFFFFFFFF),
+                     (OM + 1, W * 4), (OM + 2, 0xFFFFFFFF), (OM + 5, 0), (OM + 6, 0), (OM + 7, 0), (OM + 8, 0), (OM + 10, 0),
+                     (OM + 11, 0), (OM + 12, 0xFF), (OM + 13, 0), (OM + 14, 0), (OM + 15, (1 << 8) | 1)]:
+            dev.dcr_write(a, v)
+        args = dev.upload(arg)
+        try:
+            dev.start(self.kernel, args)
+            dev.ready_wait()
+            return self.cbuf.read(np.empty((W, W), np.uint32))
+        finally:
+            args.free()
+
+    def upload(self, data):
+        b = self.dev.alloc(max(len(data), 4), self.vx.VX_MEM_READ)
+        b.write(np.frombuffer(bytes(data), np.uint8))
+        return b
+
+    def close(self):
+        self.dev.close()
+
+
+def test_tile_buffers_of_another_tile_size_are_refused(d3, native):
+    """The kernel is built for 32 x 32 tiles and the buffer formats do not say what they were binned with: a buffer that
+    vx_cuda_draw3d_binning made at another size, or one the app declares in VX_DCR_RASTER_EXT_TILE_LOGSIZE, fails
+    vx_start instead of rendering garbage."""
+    import ctypes as C
+
+    from skybox_rt_b200 import vortex as vx
+    r = RawDraw(d3, native)
+    try:
+        gold = od.golden_framebuffer(os.path.join(od.GOLDEN_DIR, "triangle_ref_64.npy"))
+        n5, tb5, pb5, _ = r.trace.binning(0, 64, 64)
+        n4, tb4, pb4, _ = r.trace.binning(0, 64, 64, tile_logsize=4)
+        t5, p5, t4, p4 = r.upload(tb5), r.upload(pb5), r.upload(tb4), r.upload(pb4)
+        assert np.array_equal(r.draw(n5, t5, p5), gold)            # undeclared: accepted as before
+        r.dev.dcr_write(d3.VX_DCR_RASTER_EXT_TILE_LOGSIZE, 4)       # host-binned at 16 x 16, declared
+        with pytest.raises(vx.VortexError):
+            r.draw(n4, t4, p4)
+        r.dev.dcr_write(d3.VX_DCR_RASTER_EXT_TILE_LOGSIZE, 5)
+        assert np.array_equal(r.draw(n5, t5, p5), gold)
+        r.dev.dcr_write(d3.VX_DCR_RASTER_EXT_TILE_LOGSIZE, 0)
+        # device-binned: the buffer itself remembers its size
+        verts, prims, near, far = r.trace.draw_arrays(0)
+        vb, pbuf = r.dev.upload(np.ascontiguousarray(verts, np.float32)), r.dev.upload(np.ascontiguousarray(prims, np.uint32))
+        for logsize, ok in ((4, False), (5, True)):
+            tb, prb, info = C.c_void_p(), C.c_void_p(), d3.BinningInfo()
+            assert vx.lib().vx_cuda_draw3d_binning(r.dev.handle, vb.handle, len(verts), pbuf.handle, len(prims), near, far, 64, 64,
+                                                   logsize, d3.TILEBUF_REFERENCE, 0, 1, C.byref(tb), C.byref(prb), C.byref(info)) == 0
+            tile, prim = vx.Buffer(r.dev, tb, info.tilebuf_size), vx.Buffer(r.dev, prb, info.primbuf_size)
+            if ok:
+                assert np.array_equal(r.draw(info.num_tiles, tile, prim), gold)
+            else:
+                with pytest.raises(vx.VortexError):
+                    r.draw(info.num_tiles, tile, prim)
+    finally:
+        r.close()
+
+
+def test_malformed_tile_and_primitive_buffers_are_reported_not_faulted(d3, native, capfd):
+    """A primitive id past the primitive buffer, a primitive list that leaves the tile buffer and a primitive buffer
+    without one whole record end as -1 from vx_ready_wait / vx_start with a message -- not as a sticky CUDA fault:
+    the next well-formed draw on the same device gives the golden frame."""
+    from skybox_rt_b200 import vortex as vx
+    r = RawDraw(d3, native)
+    try:
+        gold = od.golden_framebuffer(os.path.join(od.GOLDEN_DIR, "triangle_ref_64.npy"))
+        n, tb, pb, _ = r.trace.binning(0, 64, 64)
+        good_t, good_p = r.upload(tb), r.upload(pb)
+        assert np.array_equal(r.draw(n, good_t, good_p), gold)
+        words = np.frombuffer(tb, np.uint32).copy()
+        bad_pid = words.copy()
+        bad_pid[2 * n] = 0x00FFFFFF                                   # first id of the first list (rast_tile_header_t = 8 B)
+        with pytest.raises(vx.VortexError):
+            r.draw(n, r.upload(bad_pid.tobytes()), good_p)
+        assert "primitive id lies outside" in capfd.readouterr().err
+        assert np.array_equal(r.draw(n, good_t, good_p), gold)        # the device is alive and the flag was cleared
+        bad_list = words.copy()
+        bad_list[2 * (n - 1) + 1] |= 0xFFFF0000                        # pids_count of the last tile = 65535
+        with pytest.raises(vx.VortexError):
+            r.draw(n, r.upload(bad_list.tobytes()), good_p)
+        assert "primitive list lies outside" in capfd.readouterr().err
+        assert np.array_equal(r.draw(n, good_t, good_p), gold)
+        with pytest.raises(vx.VortexError):                            # 64 bytes hold no 120-byte record: refused at vx_start
+            r.draw(n, good_t, r.upload(pb[:64]))
+        assert np.array_equal(r.draw(n, good_t, good_p), gold)
+    finally:
+        r.close()
