@@ -158,12 +158,17 @@ static int fork_ranks(int argc, char** argv) {
   }
   for (r = 0; r < num_gpus; ++r) {
     pid_t done = wait(&status);
-    uint32_t k;
+    uint32_t k, who = num_gpus;
     if (done < 0) { rc = -1; continue; }
     for (k = 0; k < num_gpus; ++k)
-      if (pids[k] == done) pids[k] = 0;
+      if (pids[k] == done) { pids[k] = 0; who = k; }
     if (WIFEXITED(status) && WEXITSTATUS(status) == 0) continue;
-    if (!rc) rc = WIFEXITED(status) ? WEXITSTATUS(status) : -1;
+    /* ranks other than 0 are silent (their stdout is /dev/null), so the parent says which one failed */
+    if (!rc) {
+      rc = WIFEXITED(status) ? WEXITSTATUS(status) : -1;
+      printf("Error: rank %u of %u failed (%s %d)\n", who, num_gpus, WIFEXITED(status) ? "exit code" : "signal",
+             WIFEXITED(status) ? WEXITSTATUS(status) : WTERMSIG(status));
+    }
     /* a rank that died leaves the others waiting in a collective: end exactly the processes started here */
     for (k = 0; k < num_gpus; ++k)
       if (pids[k] > 0) kill(pids[k], SIGTERM);

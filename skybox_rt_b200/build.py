@@ -108,7 +108,7 @@ def build(force=False, verbose=False):
     d3_dir = os.path.join(PKG, "apps", "draw3d")
     d3_lib_src = [os.path.join(d3_dir, "draw3d_app.c")]
     d3_so = os.path.join(LIB, "libdraw3d_app.so")
-    link = ["-L", LIB, "-lvortex", "-lskybox_rt_host", "-lz", "-lm"]
+    link = ["-pthread", "-L", LIB, "-lvortex", "-lskybox_rt_host", "-lz", "-lm"]
     if force or _stale(d3_so, d3_lib_src + headers + [os.path.join(d3_dir, "draw3d_app.h"), vx_so, host_so]):
         _run([CC] + HOST_CFLAGS + ["-shared", "-o", d3_so] + d3_lib_src + link + ["-Wl,-rpath,$ORIGIN"], verbose)
     exe = os.path.join(BIN, "draw3d")

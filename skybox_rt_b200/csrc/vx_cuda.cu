@@ -107,7 +107,8 @@ int vx_dev_open(vx_device_h* hdevice) {
   dev->copy_stream = nullptr;
   dev->copy_next_ticket = 0;
   dev->stage_ring = nullptr;
-  dev->stage_next = 0;
+  dev->stage_head = dev->stage_count = 0;
+  dev->stage_tail = 0;
   dev->last_raster_tiles = 0;
   dev->last_raster_fragments = dev->last_raster_tests = 0;
   dev->run_recorded = false;
@@ -247,6 +248,29 @@ int vx_mem_info(vx_device_h hdevice, uint64_t* mem_free, uint64_t* mem_used) {
   return 0;
 }
 
+// Staged uploads travel by a copy KERNEL that reads the page-locked ring through its device mapping, not by a DMA
+// transfer: a copy engine that is busy with a 64 MB read-back on the second stream (vx_cuda_copy_from_dev_async) takes
+// the launch stream's small host-to-device transfers only after it -- measured on B200: every frame of a pipelined
+// render loop waited for the previous frame's read-back (1.19 + 0.65 ms instead of 1.19) -- while SM loads over PCIe
+// are independent of the engines.  VX_CUDA_STAGE_KERNEL=0 restores cudaMemcpyAsync (A/B).
+namespace {
+__global__ void __launch_bounds__(256) stage_copy_kernel(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint64_t n) {
+  const uint64_t tid = (uint64_t)blockIdx.x * 256u + threadIdx.x, nth = (uint64_t)gridDim.x * 256u;
+  uint64_t done = 0;
+  if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {  // src is a 256-byte granule of the ring
+    const uint64_t n16 = n >> 4;
+    for (uint64_t i = tid; i < n16; i += nth) reinterpret_cast<uint4*>(dst)[i] = __ldcv(reinterpret_cast<const uint4*>(src) + i);
+    done = n16 << 4;
+  }
+  for (uint64_t i = done + tid; i < n; i += nth) dst[i] = __ldcv(src + i);
+}
+}  // namespace
+
+static bool stage_kernel_enabled() {
+  static const bool on = env_int("VX_CUDA_STAGE_KERNEL", 1) != 0;
+  return on;
+}
+
 static bool staged_uploads_enabled() {  // VX_CUDA_STAGED_UPLOADS=0: every upload blocks on the stream (A/B)
   static const bool on = env_int("VX_CUDA_STAGED_UPLOADS", 1) != 0;
   return on;
@@ -258,32 +282,70 @@ int vx_copy_to_dev(vx_buffer_h hbuffer, const void* host_ptr, uint64_t dst_offse
   if (dst_offset + size > b->size) return -1;  // callbacks.inc:155-156
   vx_device* dev = b->dev;
   VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
-  if (b->shadow) {
-    // small host-written buffers (kernel arguments, kernel images): the bytes go to the shadow first and travel from
-    // there.  The shadow is pageable memory, which cudaMemcpyAsync stages before it returns, so the caller's buffer
-    // and the shadow are both free on return WITHOUT waiting for the frames still queued on the stream -- a render
-    // loop that uploads a new kernel_arg_t per frame keeps the device busy.
-    memcpy(b->shadow + dst_offset, host_ptr, size);
-    VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, b->shadow + dst_offset, size, cudaMemcpyHostToDevice, dev->stream));
-  } else if (size <= kStageSlotBytes && staged_uploads_enabled()) {
-    // Medium uploads (a draw's tile / primitive buffers, textures): the bytes are copied into a slot of a page-locked
-    // ring and travel from there, queued on the launch stream behind the kernels already in it.  The caller's buffer
-    // is free on return, as the reference's blocking copy promises (runtime/simx/vortex.cpp:138-153), but the host
-    // does not wait for the device: it goes on binning the next draw while this one renders.  A slot is reused
-    // only after the transfer that read it last has completed.
+  // small host-written buffers (kernel arguments, kernel images) keep a host shadow: vx_start decodes from it
+  if (b->shadow) memcpy(b->shadow + dst_offset, host_ptr, size);
+  if (size <= kStageSlotBytes && staged_uploads_enabled()) {
+    // Small and medium uploads (kernel arguments, a draw's tile / primitive buffers, textures): the bytes are copied
+    // into a page-locked ring and travel from there, queued on the launch stream behind the kernels already in it.
+    // The caller's buffer is free on return, as the reference's blocking copy promises
+    // (runtime/simx/vortex.cpp:138-153), but the host does not wait for the device: it goes on binning the next draws
+    // -- and, the ring being 32 MiB handed out by the byte, the next frames -- while this one renders.
     if (!dev->stage_ring) {
-      VX_CUDA_OK(cudaHostAlloc(&dev->stage_ring, kStageSlots * kStageSlotBytes, cudaHostAllocDefault));
+      VX_CUDA_OK(cudaHostAlloc(&dev->stage_ring, kStageRingBytes, cudaHostAllocMapped));
+      void* mapped = nullptr;  // unified addressing: the device sees the ring at its host address
+      if (cudaHostGetDevicePointer(&mapped, dev->stage_ring, 0) != cudaSuccess || mapped != dev->stage_ring) {
+        cudaGetLastError();
+        dev->stage_mapped = false;
+      } else {
+        dev->stage_mapped = true;
+      }
       for (cudaEvent_t& e : dev->stage_done) VX_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-      dev->stage_next = 0;
+      dev->stage_head = dev->stage_count = 0;
+      dev->stage_tail = 0;
     }
-    const uint32_t slot = dev->stage_next % kStageSlots;
-    if (dev->stage_next >= (uint32_t)kStageSlots) VX_CUDA_OK(cudaEventSynchronize(dev->stage_done[slot]));
-    uint8_t* stage = dev->stage_ring + (uint64_t)slot * kStageSlotBytes;
+    const uint64_t need = size ? (size + 255) & ~255ull : 256;
+    auto retire_oldest = [&]() {
+      dev->stage_head = (dev->stage_head + 1) % kStageEntries;
+      --dev->stage_count;
+    };
+    // transfers that have finished give their bytes back without any waiting
+    while (dev->stage_count && cudaEventQuery(dev->stage_done[dev->stage_head]) == cudaSuccess) retire_oldest();
+    if (dev->stage_count == 0) dev->stage_tail = 0;
+    uint64_t off = dev->stage_tail;
+    if (off + need > kStageRingBytes) off = 0;  // no transfer wraps around the end of the ring
+    auto in_use = [&]() {
+      for (uint32_t i = 0; i < dev->stage_count; ++i) {
+        const auto& e = dev->stage_span[(dev->stage_head + i) % kStageEntries];
+        if (off < e.end && e.begin < off + need) return true;
+      }
+      return false;
+    };
+    // the bytes are reused only after every transfer that reads them has completed (oldest first: stream order)
+    while (dev->stage_count && (dev->stage_count == (uint32_t)kStageEntries || in_use())) {
+      VX_CUDA_OK(cudaEventSynchronize(dev->stage_done[dev->stage_head]));
+      retire_oldest();
+    }
+    uint8_t* stage = dev->stage_ring + off;
     memcpy(stage, host_ptr, size);
-    VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, stage, size, cudaMemcpyHostToDevice, dev->stream));
+    if (dev->stage_mapped && stage_kernel_enabled() && size > 0) {
+      const uint64_t units = (size + 15) / 16;
+      const unsigned cap = (unsigned)dev->prop.multiProcessorCount * 8u;
+      const unsigned grid = (unsigned)((units + 255) / 256 < cap ? (units + 255) / 256 : cap);
+      stage_copy_kernel<<<grid, 256, 0, dev->stream>>>((uint8_t*)b->dptr + dst_offset, stage, size);
+      VX_CUDA_OK(cudaGetLastError());
+    } else {
+      VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, stage, size, cudaMemcpyHostToDevice, dev->stream));
+    }
+    const uint32_t slot = (dev->stage_head + dev->stage_count) % kStageEntries;
     VX_CUDA_OK(cudaEventRecord(dev->stage_done[slot], dev->stream));
-    dev->stage_next++;
-    if (dev->stage_next >= 2u * kStageSlots) dev->stage_next -= kStageSlots;  // keep ">= kStageSlots" true, no overflow
+    dev->stage_span[slot].begin = off;
+    dev->stage_span[slot].end = off + need;
+    ++dev->stage_count;
+    dev->stage_tail = off + need;
+  } else if (b->shadow) {
+    // VX_CUDA_STAGED_UPLOADS=0: the shadow is pageable memory, which cudaMemcpyAsync stages before it returns, so the
+    // caller's buffer and the shadow are both free on return without waiting for the frames queued on the stream
+    VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, b->shadow + dst_offset, size, cudaMemcpyHostToDevice, dev->stream));
   } else {
     VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, host_ptr, size, cudaMemcpyHostToDevice, dev->stream));
     VX_CUDA_OK(cudaStreamSynchronize(dev->stream));

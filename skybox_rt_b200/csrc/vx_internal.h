@@ -33,8 +33,9 @@ struct vx_buffer {
 };
 
 constexpr uint64_t kShadowMaxBytes = 4096;
-constexpr int kStageSlots = 8;
-constexpr uint64_t kStageSlotBytes = 4ull << 20;
+constexpr uint64_t kStageSlotBytes = 4ull << 20;   // largest upload that is staged
+constexpr uint64_t kStageRingBytes = 32ull << 20;  // page-locked staging ring, allocated by the byte (256-byte granules)
+constexpr int kStageEntries = 256;                 // staged transfers that may be in flight
 
 // Device-side counters written by the kernels (one u64 each).
 enum {
@@ -69,10 +70,15 @@ struct vx_device {
   cudaEvent_t copy_done[16];
   uint64_t copy_next_ticket;
   // staged uploads (vx_copy_to_dev of up to kStageSlotBytes): page-locked ring the caller's bytes are copied into, so
-  // that the transfer is queued on the launch stream and the host does not wait for the kernels in front of it
-  uint8_t* stage_ring;          // kStageSlots x kStageSlotBytes, cudaHostAlloc'ed at the first staged upload
-  cudaEvent_t stage_done[8];
-  uint32_t stage_next;
+  // that the transfer is queued on the launch stream and the host does not wait for the kernels in front of it.  The
+  // ring is handed out by the byte: a frame of small uploads (a draw's tile / primitive buffers are tens of KB) takes
+  // a few MB, so the host can run several frames ahead of the device before it has to wait for a transfer
+  uint8_t* stage_ring;          // kStageRingBytes, cudaHostAlloc'ed at the first staged upload
+  bool stage_mapped;            // the ring is visible to kernels at its host address (copy kernel instead of DMA)
+  cudaEvent_t stage_done[kStageEntries];                        // FIFO of the transfers in flight: completion event ...
+  struct { uint64_t begin, end; } stage_span[kStageEntries];   // ... and the bytes of the ring each one reads
+  uint32_t stage_head, stage_count;                             // oldest entry, entries in flight
+  uint64_t stage_tail;                                          // end of the newest entry's bytes
   bool run_recorded;            // ev_start/ev_stop bracket the last vx_start
   std::map<uint32_t, uint32_t> dcrs;
   vx_buffer* buffers;           // intrusive list of live allocations

@@ -49,4 +49,4 @@ def test_multi_rank_app_reports_a_failed_rank_as_its_exit_code(native, tmp_path)
     env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
     r = subprocess.run([app(native), "-g", "2", "-o", str(tmp_path / "o.png")], capture_output=True, text=True, timeout=120, env=env)
     assert r.returncode != 0
-    assert "vx_dev_open" in r.stdout
+    assert "failed (exit code" in r.stdout  # the parent names the rank: ranks other than 0 print nothing themselves

@@ -98,6 +98,33 @@ def test_auto_flow_and_async_read_back_equal_the_reference_flow(d3, name, w, h):
             a.close()
 
 
+@pytest.mark.parametrize("name", ["vase", "mouse", "scene", "tekkaman"])
+def test_auto_flow_bins_on_worker_threads_without_changing_a_word(d3, name):
+    """Under SRT_DRAW3D_AUTO the host pre-pass of a frame's draws runs on a thread pool beside the submission
+    (apps/draw3d/draw3d_app.c: bin_pool_t).  Ten frames in a row, then draw ranges (render(start, end), which is how
+    the per-draw measurements drive it), must equal the serial reference flow in colour and depth."""
+    t = d3.Trace(blob=od.trace_blob(name))
+    w, h = 640, 400
+    n = t.num_drawcalls
+    with d3.Draw3D(w, h, flags=ALL_SW) as app:
+        ref, zref = app.frame(t, depth=True)
+        app.clear()
+        app.render(t, 0, n // 2)
+        half, zhalf = app.read(depth=True)
+    with d3.Draw3D(w, h, flags=ALL_SW | d3.AUTO) as app:
+        for i in range(10):
+            fb, zb = app.frame(t, depth=True)
+            assert np.array_equal(fb, ref) and np.array_equal(zb, zref), i
+        app.clear()
+        app.render(t, 0, n // 2)
+        fb, zb = app.read(depth=True)
+        assert np.array_equal(fb, half) and np.array_equal(zb, zhalf)
+        if n > 1:
+            app.render(t, n // 2 + 1, n - 1)  # the rest of the frame on top
+            fb, zb = app.read(depth=True)
+            assert np.array_equal(fb, ref) and np.array_equal(zb, zref)
+
+
 @pytest.mark.parametrize("name", ["evilskull", "polybump"])
 def test_prepared_resubmission_equals_per_draw_render(d3, name):
     t = d3.Trace(blob=od.trace_blob(name))

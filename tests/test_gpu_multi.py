@@ -113,3 +113,41 @@ def test_two_ranks_gathered_through_the_c_abi_equal_the_single_gpu_frame(native,
                         os.path.join(ROOT, "tests", "_multi_driver.py"), kind], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "0 words differ" in r.stdout
+
+
+@pytest.mark.gpu
+def test_staged_uploads_keep_their_bytes_when_the_host_runs_far_ahead(native):
+    """vx_copy_to_dev of up to 4 MiB copies into a page-locked ring (32 MiB, handed out by the byte, 256 transfers in
+    flight) and returns before the transfer ran.  Far more bytes than the ring holds are uploaded back to back behind a
+    slow kernel, sizes from 1 byte to the staging limit and just above it: every buffer must read back exactly what
+    was passed, i.e. no bytes of the ring are reused before the transfer that reads them has completed."""
+    from skybox_rt_b200 import raytrace as rt
+    from skybox_rt_b200 import vortex as vx
+    rng = np.random.default_rng(7)
+    sizes = [1, 3, 255, 256, 257, 4096, 4097, 70000, (4 << 20) - 1, 4 << 20, 3 << 20, 1 << 20]
+    sizes += [int(s) for s in rng.integers(1, 600000, 330)] + [4 << 20] * 12 + [int(s) for s in rng.integers(1, 5000, 300)]
+    sizes += [(4 << 20) + 4]  # above the staging limit: the blocking path, last because it drains the stream
+    nodes, tris = rt.build_bvh2(rt.scene_terrain(120, 100))
+    with rt.RayTracer(nodes, tris) as tracer:
+        dev = tracer.dev
+        # something slow in front of the uploads so that they queue up instead of completing at once
+        tracer.render(rt.make_arg(1920, 1080, 2, spp=1, seed=1, scene="terrain"))  # allocates the target and the arguments
+        arg = rt.make_arg(1920, 1080, 2, spp=4, seed=1, scene="terrain")
+        tracer._bind(arg, 1920 * 1080 * 4)
+        tracer.args.write(arg)
+        dev.start(tracer.kernel, tracer.args)
+        bufs, want = [], []
+        for i, n in enumerate(sizes):
+            data = rng.integers(0, 256, n, dtype=np.uint8)
+            b = dev.alloc(n, vx.VX_MEM_READ)
+            b.write(data)
+            data_copy = data.copy()
+            data[:] = 0xEE  # the caller's buffer is free on return: scribbling on it must not reach the device
+            bufs.append(b)
+            want.append(data_copy)
+        assert sum(sizes) > 3 * (32 << 20)
+        for b, w in zip(bufs, want):
+            got = np.empty(len(w), np.uint8)
+            b.read(got)
+            assert np.array_equal(got, w), len(w)
+            b.free()
