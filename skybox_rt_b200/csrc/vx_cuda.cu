@@ -249,10 +249,9 @@ int vx_mem_info(vx_device_h hdevice, uint64_t* mem_free, uint64_t* mem_used) {
 }
 
 // Staged uploads travel by a copy KERNEL that reads the page-locked ring through its device mapping, not by a DMA
-// transfer: a copy engine that is busy with a 64 MB read-back on the second stream (vx_cuda_copy_from_dev_async) takes
-// the launch stream's small host-to-device transfers only after it -- measured on B200: every frame of a pipelined
-// render loop waited for the previous frame's read-back (1.19 + 0.65 ms instead of 1.19) -- while SM loads over PCIe
-// are independent of the engines.  VX_CUDA_STAGE_KERNEL=0 restores cudaMemcpyAsync (A/B).
+// transfer: SM loads over PCIe leave the copy engines to the read-back that runs beside a render loop on the second
+// stream (vx_cuda_copy_from_dev_async).  Measured on B200 the two are equal for the raster loop (1.84 against 1.86 ms
+// per frame, profiles/r02d_draw3d_e2e_timeline*.txt); VX_CUDA_STAGE_KERNEL=0 selects cudaMemcpyAsync (A/B).
 namespace {
 __global__ void __launch_bounds__(256) stage_copy_kernel(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint64_t n) {
   const uint64_t tid = (uint64_t)blockIdx.x * 256u + threadIdx.x, nth = (uint64_t)gridDim.x * 256u;
@@ -282,10 +281,15 @@ int vx_copy_to_dev(vx_buffer_h hbuffer, const void* host_ptr, uint64_t dst_offse
   if (dst_offset + size > b->size) return -1;  // callbacks.inc:155-156
   vx_device* dev = b->dev;
   VX_CUDA_OK(cudaSetDevice(dev->cuda_dev));
-  // small host-written buffers (kernel arguments, kernel images) keep a host shadow: vx_start decodes from it
-  if (b->shadow) memcpy(b->shadow + dst_offset, host_ptr, size);
-  if (size <= kStageSlotBytes && staged_uploads_enabled()) {
-    // Small and medium uploads (kernel arguments, a draw's tile / primitive buffers, textures): the bytes are copied
+  if (b->shadow) {
+    // small host-written buffers (kernel arguments, kernel images): the bytes go to the shadow first (vx_start decodes
+    // from it) and travel from there.  The shadow is pageable memory, which cudaMemcpyAsync stages before it returns,
+    // so the caller's buffer and the shadow are both free on return WITHOUT waiting for the frames still queued on the
+    // stream -- a render loop that uploads a new kernel_arg_t per frame keeps the device busy.
+    memcpy(b->shadow + dst_offset, host_ptr, size);
+    VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, b->shadow + dst_offset, size, cudaMemcpyHostToDevice, dev->stream));
+  } else if (size <= kStageSlotBytes && staged_uploads_enabled()) {
+    // Medium uploads (a draw's tile / primitive buffers, textures, a packed frame): the bytes are copied
     // into a page-locked ring and travel from there, queued on the launch stream behind the kernels already in it.
     // The caller's buffer is free on return, as the reference's blocking copy promises
     // (runtime/simx/vortex.cpp:138-153), but the host does not wait for the device: it goes on binning the next draws
@@ -342,10 +346,6 @@ int vx_copy_to_dev(vx_buffer_h hbuffer, const void* host_ptr, uint64_t dst_offse
     dev->stage_span[slot].end = off + need;
     ++dev->stage_count;
     dev->stage_tail = off + need;
-  } else if (b->shadow) {
-    // VX_CUDA_STAGED_UPLOADS=0: the shadow is pageable memory, which cudaMemcpyAsync stages before it returns, so the
-    // caller's buffer and the shadow are both free on return without waiting for the frames queued on the stream
-    VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, b->shadow + dst_offset, size, cudaMemcpyHostToDevice, dev->stream));
   } else {
     VX_CUDA_OK(cudaMemcpyAsync((char*)b->dptr + dst_offset, host_ptr, size, cudaMemcpyHostToDevice, dev->stream));
     VX_CUDA_OK(cudaStreamSynchronize(dev->stream));
